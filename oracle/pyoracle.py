@@ -1,0 +1,153 @@
+"""ctypes binding of the CPU oracle (TEST INFRASTRUCTURE ONLY).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module; nothing under chanamq_b200/ does.  See oracle/trie_compat.hpp for what it restates.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+DIRECT, FANOUT, TOPIC, HEADERS = 0, 1, 2, 3
+COMPAT, SPEC = 0, 1
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(path):
+            build()
+        L = C.CDLL(path)
+        u8p, u32p = C.POINTER(C.c_uint8), C.POINTER(C.c_uint32)
+        L.orc_new.restype = C.c_void_p
+        L.orc_new.argtypes = [C.c_int, C.c_int]
+        L.orc_free.argtypes = [C.c_void_p]
+        L.orc_set_inplace.argtypes = [C.c_void_p, C.c_int]
+        for f in (L.orc_bind, L.orc_unbind):
+            f.restype = C.c_int
+            f.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_int]
+        L.orc_n_queues.restype = C.c_uint32
+        L.orc_n_queues.argtypes = [C.c_void_p]
+        L.orc_queue_name.restype = C.c_int
+        L.orc_queue_name.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), u32p]
+        L.orc_route.restype = C.c_int64
+        L.orc_route.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int]
+        L.orc_offsets.restype = C.c_void_p
+        L.orc_ids.restype = C.c_void_p
+        L.orc_durable.restype = C.c_void_p
+        L.orc_err.restype = C.c_void_p
+        for f in (L.orc_offsets, L.orc_ids, L.orc_durable, L.orc_err):
+            f.argtypes = [C.c_void_p]
+        L.orc_last_seconds.restype = C.c_double
+        L.orc_last_seconds.argtypes = [C.c_void_p]
+        L.orc_pair_match.restype = C.c_int
+        L.orc_pair_match.argtypes = [C.c_int, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32]
+        L.orc_split.restype = C.c_int
+        L.orc_split.argtypes = [C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, u32p]
+        _LIB = L
+    return _LIB
+
+
+def _b(s):
+    return s if isinstance(s, (bytes, bytearray)) else s.encode("utf-8")
+
+
+def pack_keys(keys):
+    """list of str/bytes -> (uint8 blob, uint32 offsets[n+1])"""
+    bs = [_b(k) for k in keys]
+    off = np.zeros(len(bs) + 1, dtype=np.uint32)
+    if bs:
+        off[1:] = np.cumsum([len(b) for b in bs], dtype=np.uint64).astype(np.uint32)
+    blob = np.frombuffer(b"".join(bs), dtype=np.uint8).copy() if bs else np.zeros(0, dtype=np.uint8)
+    return blob, off
+
+
+def split(s):
+    s = _b(s)
+    out = C.create_string_buffer(len(s) + 1)
+    n = C.c_uint32(0)
+    cnt = lib().orc_split(s, len(s), out, len(s) + 1, C.byref(n))
+    if cnt <= 0:
+        return []
+    return out.raw[: n.value].split(b"\n")
+
+
+def pair_match(mode, pattern, key):
+    p, k = _b(pattern), _b(key)
+    return lib().orc_pair_match(mode, p, len(p), k, len(k))
+
+
+class Oracle:
+    """One exchange's matcher, restated from the reference (trait QueueMatcher, QueueMatcher.scala:11-27)."""
+
+    def __init__(self, exchange_type=TOPIC, mode=COMPAT, inplace=False):
+        self.L = lib()
+        self.h = self.L.orc_new(exchange_type, mode)
+        if inplace:
+            self.L.orc_set_inplace(self.h, 1)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_free(self.h)
+            self.h = None
+
+    def bind(self, key, queue, durable=False):
+        k, q = _b(key), _b(queue)
+        return self.L.orc_bind(self.h, k, len(k), q, len(q), int(durable))
+
+    def unbind(self, key, queue, durable=False):
+        k, q = _b(key), _b(queue)
+        return self.L.orc_unbind(self.h, k, len(k), q, len(q), int(durable))
+
+    def n_queues(self):
+        return self.L.orc_n_queues(self.h)
+
+    def queue_name(self, qid):
+        p, n = C.c_void_p(), C.c_uint32()
+        if self.L.orc_queue_name(self.h, qid, C.byref(p), C.byref(n)) != 0:
+            raise IndexError(qid)
+        return C.string_at(p, n.value)
+
+    def queue_names(self):
+        return [self.queue_name(i) for i in range(self.n_queues())]
+
+    def route_packed(self, blob, off, threads=1):
+        """-> (offsets u32[n+1], ids u32[total], any_durable u8[n], err u8[n]) as numpy copies"""
+        n = len(off) - 1
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.uint32)
+        total = self.L.orc_route(self.h, blob.ctypes.data, off.ctypes.data, n, threads)
+        if total < 0:
+            raise RuntimeError("oracle route overflow")
+
+        def arr(ptr, count, dt):
+            if count == 0:
+                return np.zeros(0, dtype=dt)
+            buf = (C.c_uint8 * (count * np.dtype(dt).itemsize)).from_address(ptr)
+            return np.frombuffer(buf, dtype=dt, count=count).copy()
+
+        return (
+            arr(self.L.orc_offsets(self.h), n + 1, np.uint32),
+            arr(self.L.orc_ids(self.h), int(total), np.uint32),
+            arr(self.L.orc_durable(self.h), n, np.uint8),
+            arr(self.L.orc_err(self.h), n, np.uint8),
+        )
+
+    def last_seconds(self):
+        return self.L.orc_last_seconds(self.h)
+
+    def route(self, keys, threads=1):
+        """-> list (per key) of sorted queue-name lists; None where the reference would throw (zero words)"""
+        blob, off = pack_keys(keys)
+        o, ids, _, err = self.route_packed(blob, off, threads)
+        names = self.queue_names()
+        return [None if err[i] else [names[j] for j in ids[o[i]:o[i + 1]]] for i in range(len(keys))]
