@@ -1,0 +1,505 @@
+// C ABI of libchanagpu.so (declarations and reference citations: include/chanamq_gpu.h).
+// Host logic only: table life cycle, staging, stream plumbing.  All matching happens in
+// kernels.cu; there is no CPU fallback — a CUDA failure is returned as CHQ_E_CUDA.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "../../include/chanamq_gpu.h"
+#include "host_table.hpp"
+#include "kernels.h"
+
+using namespace chq;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CU(call)                                                                                  \
+  do {                                                                                            \
+    cudaError_t e__ = (call);                                                                     \
+    if (e__ != cudaSuccess)                                                                       \
+      return fail(CHQ_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));               \
+  } while (0)
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t cap = 0;  // elements
+  int ensure(size_t need) {
+    if (need <= cap) return CHQ_OK;
+    if (p) CU(cudaFree(p));
+    p = nullptr;
+    cap = 0;
+    size_t want = need + need / 4 + 64;
+    CU(cudaMalloc(&p, want * sizeof(T)));
+    cap = want;
+    return CHQ_OK;
+  }
+  int upload(const T* src, size_t n, cudaStream_t st) {
+    int rc = ensure(n ? n : 1);
+    if (rc) return rc;
+    if (n) CU(cudaMemcpyAsync(p, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
+    return CHQ_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+template <typename T>
+struct PinBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t need) {
+    if (need <= cap) return CHQ_OK;
+    if (p) CU(cudaFreeHost(p));
+    p = nullptr;
+    cap = 0;
+    size_t want = need + need / 4 + 64;
+    CU(cudaMallocHost(&p, want * sizeof(T)));
+    cap = want;
+    return CHQ_OK;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+// scratch a route launch needs beyond its inputs and outputs
+struct Workspace {
+  DevBuf<uint32_t> wid;
+  DevBuf<uint8_t> nwords;
+  DevBuf<uint64_t> state;   // [0..1] = control words, [2..] = per-tile scan state
+  DevBuf<uint32_t> scratch;
+  size_t scratch_want = 16u << 20;
+  void release() { wid.release(); nwords.release(); state.release(); scratch.release(); }
+};
+
+struct RouteSlot {
+  cudaStream_t st = nullptr;
+  cudaEvent_t meta_done = nullptr;
+  Workspace ws;
+  PinBuf<uint8_t> h_blob;
+  PinBuf<uint32_t> h_off;
+  DevBuf<uint8_t> d_blob;
+  DevBuf<uint32_t> d_off;
+  DevBuf<uint32_t> d_offsets, d_ids;
+  DevBuf<uint8_t> d_durable, d_err;
+  DevBuf<uint64_t> d_total;   // [0] total, [1] status (as int32 in low word)
+  PinBuf<uint32_t> r_offsets, r_ids;
+  PinBuf<uint8_t> r_durable, r_err;
+  PinBuf<uint64_t> r_total;
+  uint32_t n = 0;
+  bool busy = false;
+  void release() {
+    ws.release(); h_blob.release(); h_off.release(); d_blob.release(); d_off.release(); d_offsets.release();
+    d_ids.release(); d_durable.release(); d_err.release(); d_total.release(); r_offsets.release();
+    r_ids.release(); r_durable.release(); r_err.release(); r_total.release();
+    if (meta_done) cudaEventDestroy(meta_done);
+    if (st) cudaStreamDestroy(st);
+  }
+};
+
+}  // namespace
+
+struct chq_table {
+  HostTable host;
+  CompiledTable ct;
+  bool committed = false;   // device copy is current: routing allowed
+  bool compiled = false;    // ct is current: queue names / stats valid
+  bool host_only = false;   // device == -1: compile-only table for host-side checks, cannot route
+  int device = 0, n_sms = 148;
+  // device copy of the compiled table
+  DevBuf<DictSlot> d_dict;
+  DevBuf<uint8_t> d_dict_bytes;
+  DevBuf<Shape> d_shapes;
+  DevBuf<uint16_t> d_exact;
+  DevBuf<Slot> d_slots;
+  DevBuf<Group> d_groups;
+  DevBuf<uint32_t> d_lits, d_rems, d_qlist;
+  TableView tv{};
+  RouteSlot slots[CHQ_SLOTS];
+  Workspace dev_ws;  // for chq_route_device
+  uint32_t max_slots = kRouteSlots, max_small = kRouteSmall;
+  uint64_t n_batches = 0, n_messages = 0, n_ids = 0;
+  std::mutex mu;  // bind may arrive from a Future callback off the actor thread (ExchangeEntity.scala:337-338)
+  chq_table(int type, int mode) : host(type, mode) {}
+};
+
+namespace {
+
+int set_device(chq_table* t) {
+  CU(cudaSetDevice(t->device));
+  return CHQ_OK;
+}
+
+int upload_table(chq_table* t) {
+  CompiledTable& c = t->ct;
+  cudaStream_t st = nullptr;
+  int rc;
+  if ((rc = t->d_dict.upload(c.dict.data(), c.dict.size(), st))) return rc;
+  if ((rc = t->d_dict_bytes.upload(c.dict_bytes.data(), c.dict_bytes.size(), st))) return rc;
+  if ((rc = t->d_shapes.upload(c.shapes.data(), c.shapes.size(), st))) return rc;
+  if ((rc = t->d_exact.upload(c.exact_rng.data(), c.exact_rng.size(), st))) return rc;
+  if ((rc = t->d_slots.upload(c.slots.data(), c.slots.size(), st))) return rc;
+  if ((rc = t->d_groups.upload(c.groups.data(), c.groups.size(), st))) return rc;
+  if ((rc = t->d_lits.upload(c.lits.data(), c.lits.size(), st))) return rc;
+  if ((rc = t->d_rems.upload(c.rems.data(), c.rems.size(), st))) return rc;
+  if ((rc = t->d_qlist.upload(c.qlist.data(), c.qlist.size(), st))) return rc;
+  CU(cudaStreamSynchronize(st));
+  TableView& v = t->tv;
+  v.dict = t->d_dict.p;
+  v.dict_bytes = t->d_dict_bytes.p;
+  v.dict_mask = (uint32_t)c.dict.size() - 1;
+  v.shapes = t->d_shapes.p;
+  v.exact_rng = t->d_exact.p;
+  v.hashy_begin = c.hashy_begin;
+  v.hashy_end = c.hashy_end;
+  v.slots = t->d_slots.p;
+  v.bucket_mask = (uint32_t)(c.slots.size() / 4) - 1;
+  v.groups = t->d_groups.p;
+  v.lits = t->d_lits.p;
+  v.rems = t->d_rems.p;
+  v.qlist = t->d_qlist.p;
+  v.wstride = c.wstride;
+  v.n_groups = (uint32_t)c.groups.size();
+  v.exchange_type = (uint32_t)t->host.type();
+  v.fanout_group = c.fanout_group;
+  return CHQ_OK;
+}
+
+// Enqueue tokenise + route for n keys already on the device.  Everything is asynchronous on st.
+int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint32_t* d_off, uint32_t n,
+                  uint32_t* d_offsets, uint32_t* d_ids, uint64_t ids_cap, uint8_t* d_durable, uint8_t* d_err,
+                  uint64_t* d_total, int32_t* d_status, cudaStream_t st) {
+  const uint32_t n_tiles = (n + kRouteThreads - 1) / kRouteThreads;
+  int rc;
+  if ((rc = ws.wid.ensure((size_t)n * t->tv.wstride + 4))) return rc;
+  if ((rc = ws.nwords.ensure((size_t)n + 1))) return rc;
+  if ((rc = ws.state.ensure((size_t)n_tiles + 2))) return rc;
+  if ((rc = ws.scratch.ensure(ws.scratch_want))) return rc;
+  CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + 2) * sizeof(uint64_t), st));
+  if (n == 0) {
+    CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
+    CU(cudaMemsetAsync(d_total, 0, sizeof(uint64_t), st));
+    CU(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+    return CHQ_OK;
+  }
+  const int split = (t->host.type() == CHQ_TOPIC || t->host.type() == CHQ_HEADERS) ? 1 : 0;
+  CU(launch_tokenize(d_blob, d_off, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
+  RouteParams p{};
+  p.tv = t->tv;
+  p.wid = ws.wid.p;
+  p.nwords = ws.nwords.p;
+  p.n = n;
+  p.n_tiles = n_tiles;
+  p.offsets = d_offsets;
+  p.ids = d_ids;
+  p.ids_cap = ids_cap;
+  p.durable = d_durable;
+  p.total = d_total;
+  p.ctrl = reinterpret_cast<uint32_t*>(ws.state.p);
+  p.tile_state = ws.state.p + 2;
+  p.scratch = ws.scratch.p;
+  p.scratch_cap = ws.scratch.cap;
+  p.max_slots = t->max_slots;
+  p.max_small = t->max_small;
+  CU(launch_route(p, t->n_sms, d_status, st));
+  t->n_batches++;
+  t->n_messages += n;
+  return CHQ_OK;
+}
+
+bool is_pinned(const void* p) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
+int slot_init(RouteSlot& s) {
+  if (!s.st) CU(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+  if (!s.meta_done) CU(cudaEventCreateWithFlags(&s.meta_done, cudaEventDisableTiming));
+  return CHQ_OK;
+}
+
+int slot_launch(chq_table* t, RouteSlot& s) {
+  int rc = enqueue_route(t, s.ws, s.d_blob.p, s.d_off.p, s.n, s.d_offsets.p, s.d_ids.p, s.d_ids.cap, s.d_durable.p,
+                         s.d_err.p, s.d_total.p, reinterpret_cast<int32_t*>(s.d_total.p + 1), s.st);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(s.r_total.p, s.d_total.p, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.st));
+  CU(cudaMemcpyAsync(s.r_offsets.p, s.d_offsets.p, ((size_t)s.n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.st));
+  if (s.n) {
+    CU(cudaMemcpyAsync(s.r_durable.p, s.d_durable.p, s.n, cudaMemcpyDeviceToHost, s.st));
+    CU(cudaMemcpyAsync(s.r_err.p, s.d_err.p, s.n, cudaMemcpyDeviceToHost, s.st));
+  }
+  CU(cudaEventRecord(s.meta_done, s.st));
+  return CHQ_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* chq_last_error(void) { return g_err.c_str(); }
+
+int32_t chq_table_create(chq_table** out, int32_t exchange_type, int32_t mode, int32_t device) {
+  if (!out || exchange_type < CHQ_DIRECT || exchange_type > CHQ_HEADERS || (mode != CHQ_MODE_COMPAT && mode != CHQ_MODE_SPEC))
+    return fail(CHQ_E_ARG, "chq_table_create: bad argument");
+  if (device < -1) return fail(CHQ_E_ARG, "chq_table_create: bad device");
+  if (device >= 0) {
+    int count = 0;
+    CU(cudaGetDeviceCount(&count));  // fails loudly when there is no GPU: no CPU path exists
+    if (device >= count) return fail(CHQ_E_ARG, "chq_table_create: no such CUDA device");
+  }
+  chq_table* t = new (std::nothrow) chq_table(exchange_type, mode);
+  if (!t) return fail(CHQ_E_ARG, "out of host memory");
+  t->device = device;
+  t->host_only = device < 0;  // compiles and reports, but every route call fails: there is no CPU matcher
+  if (!t->host_only) {
+    cudaDeviceProp prop{};
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+      delete t;
+      return fail(CHQ_E_CUDA, "cudaGetDeviceProperties failed");
+    }
+    t->n_sms = prop.multiProcessorCount;
+  }
+  *out = t;
+  return CHQ_OK;
+}
+
+int32_t chq_table_destroy(chq_table* t) {
+  if (!t) return CHQ_OK;
+  if (t->host_only) { delete t; return CHQ_OK; }
+  cudaSetDevice(t->device);
+  cudaDeviceSynchronize();
+  for (auto& s : t->slots) s.release();
+  t->dev_ws.release();
+  t->d_dict.release(); t->d_dict_bytes.release(); t->d_shapes.release(); t->d_exact.release();
+  t->d_slots.release(); t->d_groups.release(); t->d_lits.release(); t->d_rems.release(); t->d_qlist.release();
+  delete t;
+  return CHQ_OK;
+}
+
+int32_t chq_bind(chq_table* t, const uint8_t* key, uint32_t key_len, const uint8_t* queue, uint32_t queue_len,
+                 uint8_t durable) {
+  if (!t || (!key && key_len) || (!queue && queue_len)) return fail(CHQ_E_ARG, "chq_bind: bad argument");
+  std::lock_guard<std::mutex> g(t->mu);
+  t->committed = t->compiled = false;
+  return t->host.bind(std::string_view((const char*)key, key_len), std::string_view((const char*)queue, queue_len), durable != 0);
+}
+
+int32_t chq_bind_many(chq_table* t, const uint8_t* keys_blob, const uint32_t* key_offsets, const uint8_t* queues_blob,
+                      const uint32_t* queue_offsets, const uint8_t* durable, uint32_t n) {
+  if (!t || !key_offsets || !queue_offsets) return fail(CHQ_E_ARG, "chq_bind_many: bad argument");
+  std::lock_guard<std::mutex> g(t->mu);
+  t->committed = t->compiled = false;
+  int first_err = CHQ_OK;
+  for (uint32_t i = 0; i < n; ++i) {
+    int rc = t->host.bind(std::string_view((const char*)keys_blob + key_offsets[i], key_offsets[i + 1] - key_offsets[i]),
+                          std::string_view((const char*)queues_blob + queue_offsets[i], queue_offsets[i + 1] - queue_offsets[i]),
+                          durable ? durable[i] != 0 : false);
+    if (rc && !first_err) first_err = rc;
+  }
+  return first_err;
+}
+
+int32_t chq_unbind(chq_table* t, const uint8_t* key, uint32_t key_len, const uint8_t* queue, uint32_t queue_len,
+                   uint8_t durable) {
+  if (!t) return fail(CHQ_E_ARG, "chq_unbind: bad argument");
+  std::lock_guard<std::mutex> g(t->mu);
+  t->committed = t->compiled = false;
+  return t->host.unbind(std::string_view((const char*)key, key_len), std::string_view((const char*)queue, queue_len), durable != 0);
+}
+
+int32_t chq_unbind_queue(chq_table* t, const uint8_t* queue, uint32_t queue_len) {
+  if (!t) return fail(CHQ_E_ARG, "chq_unbind_queue: bad argument");
+  std::lock_guard<std::mutex> g(t->mu);
+  t->committed = t->compiled = false;
+  return t->host.unbind_queue(std::string_view((const char*)queue, queue_len));
+}
+
+int32_t chq_commit(chq_table* t) {
+  if (!t) return fail(CHQ_E_ARG, "chq_commit: bad argument");
+  std::lock_guard<std::mutex> g(t->mu);
+  if (t->host_only) {
+    t->host.compile(t->ct);
+    t->compiled = true;
+    return CHQ_OK;
+  }
+  int rc = set_device(t);
+  if (rc) return rc;
+  CU(cudaDeviceSynchronize());  // nothing in flight may still read the old table
+  t->host.compile(t->ct);
+  t->compiled = true;
+  if ((rc = upload_table(t))) return rc;
+  t->committed = true;
+  return CHQ_OK;
+}
+
+int32_t chq_n_queues(const chq_table* t, uint32_t* n) {
+  if (!t || !n) return fail(CHQ_E_ARG, "chq_n_queues: bad argument");
+  if (!t->compiled) return fail(CHQ_E_NOT_COMMITTED, "table not committed");
+  *n = (uint32_t)t->ct.queue_names.size();
+  return CHQ_OK;
+}
+
+int32_t chq_queue_name(const chq_table* t, uint32_t queue_id, const uint8_t** name, uint32_t* len) {
+  if (!t || !name || !len) return fail(CHQ_E_ARG, "chq_queue_name: bad argument");
+  if (!t->compiled) return fail(CHQ_E_NOT_COMMITTED, "table not committed");
+  if (queue_id >= t->ct.queue_names.size()) return fail(CHQ_E_ARG, "chq_queue_name: id out of range");
+  *name = (const uint8_t*)t->ct.queue_names[queue_id].data();
+  *len = (uint32_t)t->ct.queue_names[queue_id].size();
+  return CHQ_OK;
+}
+
+int32_t chq_route_submit(chq_table* t, int32_t slot, const uint8_t* keys_blob, const uint32_t* key_offsets, uint32_t n) {
+  if (!t || slot < 0 || slot >= CHQ_SLOTS || (n && (!key_offsets))) return fail(CHQ_E_ARG, "chq_route_submit: bad argument");
+  if (t->host_only) return fail(CHQ_E_CUDA, "chq_route: host-only table (device -1) cannot route; there is no CPU matcher");
+  if (!t->committed) return fail(CHQ_E_NOT_COMMITTED, "chq_route: table has uncommitted binds (call chq_commit)");
+  int rc = set_device(t);
+  if (rc) return rc;
+  RouteSlot& s = t->slots[slot];
+  if ((rc = slot_init(s))) return rc;
+  if (s.busy) CU(cudaStreamSynchronize(s.st));
+  s.n = n;
+  const size_t blob_len = n ? key_offsets[n] : 0;
+  if ((rc = s.d_blob.ensure(blob_len + 16))) return rc;
+  if ((rc = s.d_off.ensure((size_t)n + 1))) return rc;
+  if ((rc = s.d_offsets.ensure((size_t)n + 1))) return rc;
+  if ((rc = s.d_durable.ensure((size_t)n + 1))) return rc;
+  if ((rc = s.d_err.ensure((size_t)n + 1))) return rc;
+  if ((rc = s.d_total.ensure(2))) return rc;
+  if ((rc = s.d_ids.ensure((size_t)n * 16 + 1024))) return rc;
+  if ((rc = s.r_total.ensure(2))) return rc;
+  if ((rc = s.r_offsets.ensure((size_t)n + 1))) return rc;
+  if ((rc = s.r_durable.ensure((size_t)n + 1))) return rc;
+  if ((rc = s.r_err.ensure((size_t)n + 1))) return rc;
+  if (n) {
+    const uint8_t* src_blob = keys_blob;
+    const uint32_t* src_off = key_offsets;
+    if (!is_pinned(keys_blob)) {
+      if ((rc = s.h_blob.ensure(blob_len + 1))) return rc;
+      memcpy(s.h_blob.p, keys_blob, blob_len);
+      src_blob = s.h_blob.p;
+    }
+    if (!is_pinned(key_offsets)) {
+      if ((rc = s.h_off.ensure((size_t)n + 1))) return rc;
+      memcpy(s.h_off.p, key_offsets, ((size_t)n + 1) * sizeof(uint32_t));
+      src_off = s.h_off.p;
+    }
+    if (blob_len) CU(cudaMemcpyAsync(s.d_blob.p, src_blob, blob_len, cudaMemcpyHostToDevice, s.st));
+    CU(cudaMemcpyAsync(s.d_off.p, src_off, ((size_t)n + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s.st));
+  }
+  if ((rc = slot_launch(t, s))) return rc;
+  s.busy = true;
+  return CHQ_OK;
+}
+
+int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
+  if (!t || slot < 0 || slot >= CHQ_SLOTS || !out) return fail(CHQ_E_ARG, "chq_route_wait: bad argument");
+  RouteSlot& s = t->slots[slot];
+  if (!s.busy) return fail(CHQ_E_ARG, "chq_route_wait: slot was not submitted");
+  int rc = set_device(t);
+  if (rc) return rc;
+  for (int attempt = 0;; ++attempt) {
+    CU(cudaEventSynchronize(s.meta_done));
+    const uint64_t total = s.r_total.p[0];
+    const int32_t status = (int32_t)(uint32_t)s.r_total.p[1];
+    if (status == CHQ_OK) break;
+    if (attempt >= 3 || total > 0xFFFFFFFFull) {
+      s.busy = false;
+      return fail(status, status == CHQ_E_SCRATCH ? "device scratch arena exhausted" : "result does not fit 2^32-1 ids");
+    }
+    // grow what was too small and run the batch again (inputs are still on the device)
+    CU(cudaStreamSynchronize(s.st));
+    if (status == CHQ_E_OVERFLOW) { if ((rc = s.d_ids.ensure(total + 1024))) return rc; }
+    else { s.ws.scratch_want = s.ws.scratch.cap * 4; }
+    if ((rc = slot_launch(t, s))) return rc;
+  }
+  const uint64_t total = s.r_total.p[0];
+  if ((rc = s.r_ids.ensure(total + 1))) return rc;
+  if (total) CU(cudaMemcpyAsync(s.r_ids.p, s.d_ids.p, total * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.st));
+  CU(cudaStreamSynchronize(s.st));
+  s.busy = false;
+  t->n_ids += total;
+  out->n = s.n;
+  out->offsets = s.r_offsets.p;
+  out->queue_ids = s.r_ids.p;
+  out->any_durable = s.r_durable.p;
+  out->err = s.r_err.p;
+  return CHQ_OK;
+}
+
+int32_t chq_route(chq_table* t, const uint8_t* keys_blob, const uint32_t* key_offsets, uint32_t n,
+                  const uint8_t* headers_blob, const uint32_t* headers_offsets, chq_result* out) {
+  (void)headers_blob;
+  (void)headers_offsets;
+  int rc = chq_route_submit(t, 0, keys_blob, key_offsets, n);
+  if (rc) return rc;
+  return chq_route_wait(t, 0, out);
+}
+
+int32_t chq_route_device(chq_table* t, const uint8_t* d_keys_blob, const uint32_t* d_key_offsets, uint32_t n,
+                         uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,
+                         uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream) {
+  if (!t || !d_offsets || !d_total || !d_status || (n && (!d_key_offsets || !d_any_durable || !d_err)))
+    return fail(CHQ_E_ARG, "chq_route_device: bad argument");
+  if (t->host_only) return fail(CHQ_E_CUDA, "chq_route_device: host-only table (device -1) cannot route");
+  if (!t->committed) return fail(CHQ_E_NOT_COMMITTED, "chq_route_device: table has uncommitted binds");
+  int rc = set_device(t);
+  if (rc) return rc;
+  return enqueue_route(t, t->dev_ws, d_keys_blob, d_key_offsets, n, d_offsets, d_queue_ids, ids_cap, d_any_durable,
+                       d_err, d_total, d_status, (cudaStream_t)stream);
+}
+
+int32_t chq_host_alloc(void** p, uint64_t bytes) {
+  if (!p) return fail(CHQ_E_ARG, "chq_host_alloc: bad argument");
+  CU(cudaMallocHost(p, bytes ? bytes : 1));
+  return CHQ_OK;
+}
+int32_t chq_host_free(void* p) {
+  if (p) CU(cudaFreeHost(p));
+  return CHQ_OK;
+}
+
+int32_t chq_stats(const chq_table* t, char* json, uint32_t cap) {
+  if (!t || !json || !cap) return fail(CHQ_E_ARG, "chq_stats: bad argument");
+  const CompiledTable& c = t->ct;
+  const uint64_t table_bytes = c.dict.size() * sizeof(DictSlot) + c.dict_bytes.size() + c.shapes.size() * sizeof(Shape) +
+                               c.slots.size() * sizeof(Slot) + c.groups.size() * sizeof(Group) +
+                               (c.lits.size() + c.rems.size() + c.qlist.size()) * 4;
+  int w = snprintf(json, cap,
+                   "{\"bindings\": %llu, \"queues\": %zu, \"groups\": %zu, \"heads\": %llu, \"shapes\": %zu, "
+                   "\"words\": %zu, \"pattern_words\": %llu, \"wstride\": %u, \"table_bytes\": %llu, "
+                   "\"batches\": %llu, \"messages\": %llu, \"ids\": %llu, \"committed\": %s}",
+                   (unsigned long long)c.n_bindings, c.queue_names.size(), c.groups.size(), (unsigned long long)c.n_heads,
+                   c.shapes.size(), (size_t)c.n_words, (unsigned long long)c.pattern_words, c.wstride,
+                   (unsigned long long)table_bytes, (unsigned long long)t->n_batches, (unsigned long long)t->n_messages,
+                   (unsigned long long)t->n_ids, t->compiled ? "true" : "false");
+  return (w < 0 || (uint32_t)w >= cap) ? fail(CHQ_E_ARG, "chq_stats: buffer too small") : CHQ_OK;
+}
+
+uint64_t chq_kernel_launches(void) { return kernel_launches() ; }
+
+int32_t chq_debug_limits(chq_table* t, uint32_t max_slots, uint32_t max_small) {
+  if (!t) return fail(CHQ_E_ARG, "chq_debug_limits: bad argument");
+  t->max_slots = (max_slots == 0 || max_slots > (uint32_t)kRouteSlots) ? kRouteSlots : max_slots;
+  t->max_small = (max_small == 0 || max_small > (uint32_t)kRouteSmall) ? kRouteSmall : max_small;
+  return CHQ_OK;
+}
+
+}  // extern "C"

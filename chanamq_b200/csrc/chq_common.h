@@ -1,0 +1,110 @@
+// Shared between the host-side table compiler and the sm_100a kernels: the layout of one
+// exchange's compiled binding table in HBM, and the hash functions both sides must agree on.
+//
+// What the table replaces: the reference's per-exchange TrieMatcher
+// (chana-mq-server/.../engine/QueueMatcher.scala:380-601) — a pointer-chasing trie walked once
+// per message.  Here the binding set is compiled into a TUPLE-SPACE index: every pattern is
+// reduced to a shape (kind, word count, which positions are literal) plus the tuple of its
+// literal word ids; one hash probe per (key, compatible shape) finds the group of bindings
+// that share that pattern, and the group carries its sorted queue-id list.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define CHQ_HD __host__ __device__ __forceinline__
+#else
+#define CHQ_HD inline
+#endif
+
+namespace chq {
+
+constexpr uint32_t kUnknownWord = 0;          // key word that no binding mentions
+constexpr uint32_t kStar = 0xFFFFFFFEu;       // '*' inside a remainder
+constexpr uint32_t kHash = 0xFFFFFFFDu;       // '#' inside a remainder (SPEC mode only)
+constexpr uint32_t kNone = 0xFFFFFFFFu;
+constexpr int kMaxIndexedWords = 16;          // a shape indexes at most the first 16 words
+constexpr int kMaxKeyBytes = 255;             // AMQP shortstr (ValueReader.scala:35-39)
+constexpr int kMaxWords = 128;                // 255 bytes hold at most 128 non-trailing words
+constexpr int kLenCap = kMaxWords + 1;
+
+enum ShapeKind : uint8_t {
+  kExact = 0,    // no '#': key must have exactly `len` words
+  kTail = 1,     // literal/'*' prefix of `len` words then only '#': key needs >= len words
+  kComplex = 2,  // anything else: prefix indexed, remainder verified by the word-level NFA
+};
+
+struct Shape {            // 16 B
+  uint64_t seed;          // per-shape hash seed
+  uint32_t lit_mask;      // bit p set = word p of the prefix is a literal (else '*')
+  uint8_t kind;
+  uint8_t len;            // number of indexed prefix words (kExact: the whole pattern)
+  uint16_t pad;
+};
+
+enum GroupFlags : uint8_t { kAnyDurable = 1, kShared = 2 };
+
+struct Group {            // 32 B, one L2 sector
+  uint32_t list_off;      // into qlist: sorted unique queue ids bound with exactly this pattern
+  uint32_t list_len;
+  uint32_t lit_off;       // into lits: the literal word ids, in position order
+  uint32_t next;          // next group with the same (shape, literal tuple) but another remainder
+  uint32_t rem_off;       // into rems: pattern words after the indexed prefix (kComplex)
+  uint16_t rem_len;
+  uint8_t nlit;
+  uint8_t flags;          // kAnyDurable: some binding's queue is durable (ExchangeEntity.scala:302)
+                          // kShared: some queue here is also bound through another group
+  uint32_t shape;
+  uint32_t pad;
+};
+
+struct Slot { uint32_t tag; uint32_t group; };   // 4 slots = one 32 B bucket; tag 0 = empty
+
+struct DictSlot {         // 32 B: one interned pattern word
+  uint64_t hash;
+  uint64_t first8;        // first 8 bytes, little-endian packed (whole word when len <= 8)
+  uint32_t len;
+  uint32_t id;            // 0 = empty slot
+  uint32_t byte_off;      // into dict_bytes, for words longer than 8 bytes
+  uint32_t pad;
+};
+
+// Device view of a committed table (all pointers are device pointers).
+struct TableView {
+  const DictSlot* dict;
+  const uint8_t* dict_bytes;
+  uint32_t dict_mask;
+  const Shape* shapes;
+  const uint16_t* exact_rng;   // [2*(kLenCap+1)]: shapes of kind kExact with len == L are [rng[2L], rng[2L+1])
+  uint32_t hashy_begin, hashy_end;   // kTail/kComplex shapes, ascending len
+  const Slot* slots;
+  uint32_t bucket_mask;
+  const Group* groups;
+  const uint32_t* lits;
+  const uint32_t* rems;
+  const uint32_t* qlist;
+  uint32_t wstride;            // word ids kept per key (multiple of 4)
+  uint32_t n_groups;
+  // direct / fanout exchanges reuse the same index: direct = one shape over the whole-key id,
+  // fanout = a single always-matching group
+  uint32_t exchange_type;
+  uint32_t fanout_group;
+};
+
+// --- hashing -------------------------------------------------------------------------------
+CHQ_HD uint64_t mix(uint64_t h, uint32_t w) {
+  h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+  return h ^ (h >> 29);
+}
+CHQ_HD uint64_t fin(uint64_t h) {
+  h ^= h >> 32;
+  h *= 0xD6E8FEB86659FD93ull;
+  h ^= h >> 32;
+  return h;
+}
+CHQ_HD uint32_t tag_of(uint64_t h) { return (uint32_t)(h >> 32) | 1u; }
+// FNV-1a over the word's bytes, one byte at a time so the tokeniser can fold it into its scan
+constexpr uint64_t kFnvBasis = 0xCBF29CE484222325ull;
+constexpr uint64_t kFnvPrime = 0x100000001B3ull;
+CHQ_HD uint64_t fnv_step(uint64_t h, uint8_t b) { return (h ^ b) * kFnvPrime; }
+
+}  // namespace chq

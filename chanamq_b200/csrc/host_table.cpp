@@ -1,0 +1,315 @@
+#include "host_table.hpp"
+
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <unordered_map>
+
+#include "../../include/chanamq_gpu.h"
+
+namespace chq {
+
+void java_split(std::string_view s, std::vector<std::string_view>& out) {
+  out.clear();
+  size_t start = 0;
+  bool dot = false;
+  for (size_t i = 0; i < s.size(); ++i) {
+    if (s[i] == '.') {
+      out.push_back(s.substr(start, i - start));
+      start = i + 1;
+      dot = true;
+    }
+  }
+  if (!dot) {
+    out.push_back(s);
+    return;
+  }
+  out.push_back(s.substr(start));
+  while (!out.empty() && out.back().empty()) out.pop_back();
+}
+
+int HostTable::check_key(std::string_view key) const {
+  if (key.size() > (size_t)kMaxKeyBytes) return CHQ_E_KEY_TOO_LONG;
+  if (type_ == CHQ_TOPIC || type_ == CHQ_HEADERS) {
+    std::vector<std::string_view> w;
+    java_split(key, w);
+    if (w.empty()) return CHQ_E_ZERO_WORDS;  // the reference throws here (QueueMatcher.scala:420)
+  }
+  return CHQ_OK;
+}
+
+int HostTable::bind(std::string_view key, std::string_view queue, bool durable) {
+  int rc = check_key(key);
+  if (rc != CHQ_OK) return rc;
+  live_.emplace(std::string(key), std::string(queue), durable);
+  return CHQ_OK;
+}
+
+int HostTable::unbind(std::string_view key, std::string_view queue, bool durable) {
+  int rc = check_key(key);
+  if (rc != CHQ_OK) return rc;
+  live_.erase(std::make_tuple(std::string(key), std::string(queue), durable));
+  return CHQ_OK;
+}
+
+int HostTable::unbind_queue(std::string_view queue) {
+  for (auto it = live_.begin(); it != live_.end();) {
+    if (std::get<1>(*it) == queue) it = live_.erase(it);
+    else ++it;
+  }
+  return CHQ_OK;
+}
+
+namespace {
+
+uint64_t word_hash(std::string_view w) {
+  uint64_t h = kFnvBasis;
+  for (unsigned char c : w) h = fnv_step(h, c);
+  return fin(h ^ ((uint64_t)w.size() << 56));
+}
+uint64_t first8(std::string_view w) {
+  uint64_t f = 0;
+  for (size_t i = 0; i < w.size() && i < 8; ++i) f |= (uint64_t)(unsigned char)w[i] << (8 * i);
+  return f;
+}
+uint32_t pow2_at_least(uint64_t x) {
+  uint32_t p = 1;
+  while (p < x) p <<= 1;
+  return p;
+}
+
+struct GroupBuild {
+  uint32_t shape_key;  // index into the unsorted shape list
+  std::vector<uint32_t> lits, rem;
+  std::vector<uint32_t> queues;
+  bool durable = false;
+};
+
+}  // namespace
+
+void HostTable::compile(CompiledTable& out) const {
+  out = CompiledTable();
+  out.n_bindings = live_.size();
+  out.exact_rng.assign(2 * (kLenCap + 1), 0);
+
+  // queue ids: rank of the name among the names that hold a binding, ascending by bytes
+  {
+    std::set<std::string_view> q;
+    for (auto& t : live_) q.insert(std::get<1>(t));
+    out.queue_names.assign(q.begin(), q.end());
+  }
+  std::unordered_map<std::string_view, uint32_t> qid;
+  qid.reserve(out.queue_names.size() * 2);
+  for (uint32_t i = 0; i < out.queue_names.size(); ++i) qid.emplace(out.queue_names[i], i);
+
+  const bool split = (type_ == CHQ_TOPIC || type_ == CHQ_HEADERS);
+  const bool spec = (mode_ == CHQ_MODE_SPEC) && split;
+
+  if (type_ == CHQ_FANOUT) {  // FanoutMatcher.lookup: every subscriber (QueueMatcher.scala:63-65)
+    out.dict.assign(1, DictSlot{});
+    out.slots.assign(4, Slot{0, 0});
+    if (!live_.empty()) {
+      Group g{};
+      g.next = kNone;
+      bool dur = false;
+      for (auto& t : live_) {
+        out.qlist.push_back(qid.at(std::get<1>(t)));
+        dur = dur || std::get<2>(t);
+      }
+      std::sort(out.qlist.begin(), out.qlist.end());
+      out.qlist.erase(std::unique(out.qlist.begin(), out.qlist.end()), out.qlist.end());
+      g.list_off = 0;
+      g.list_len = (uint32_t)out.qlist.size();
+      g.flags = dur ? kAnyDurable : 0;
+      out.groups.push_back(g);
+      out.fanout_group = 0;
+    }
+    out.n_heads = out.groups.size();
+    return;
+  }
+
+  // pass 1: intern literal words (ids 1.. in byte order, so a rebuild gives the same table)
+  std::map<std::string_view, uint32_t> words;
+  std::vector<std::string_view> w;
+  auto is_star = [](std::string_view s) { return s.size() == 1 && s[0] == '*'; };
+  auto is_hash = [&](std::string_view s) { return spec && s.size() == 1 && s[0] == '#'; };
+  for (auto& t : live_) {
+    std::string_view key = std::get<0>(t);
+    if (split) java_split(key, w);
+    else { w.clear(); w.push_back(key); }   // DirectMatcher: whole-key equality (QueueMatcher.scala:45-47)
+    for (auto& x : w)
+      if (!split || (!is_star(x) && !is_hash(x))) words.emplace(x, 0);
+  }
+  {
+    uint32_t id = 1;
+    for (auto& kv : words) kv.second = id++;
+    out.n_words = words.size();
+  }
+
+  // pass 2: reduce every pattern to (shape, literal tuple, remainder) and group equal ones
+  std::map<std::tuple<uint8_t, uint8_t, uint32_t>, uint32_t> shape_ids;  // (kind, len, mask)
+  std::vector<std::tuple<uint8_t, uint8_t, uint32_t>> shape_list;
+  std::map<std::vector<uint32_t>, uint32_t> group_ids;  // encoded pattern -> group
+  std::vector<GroupBuild> gb;
+  std::vector<uint32_t> pat, enc;
+  bool any_complex = false;
+  uint32_t max_len = 1;
+  for (auto& t : live_) {
+    std::string_view key = std::get<0>(t);
+    if (split) java_split(key, w);
+    else { w.clear(); w.push_back(key); }
+    pat.clear();
+    for (auto& x : w) {
+      if (split && is_star(x)) pat.push_back(kStar);
+      else if (is_hash(x)) {
+        if (pat.empty() || pat.back() != kHash) pat.push_back(kHash);  // "#.#" == "#"
+      } else pat.push_back(words.at(x));
+    }
+    out.pattern_words += pat.size();
+    size_t first_hash = std::find(pat.begin(), pat.end(), kHash) - pat.begin();
+    size_t prefix = first_hash;  // == pat.size() when there is no '#'
+    size_t ip = std::min<size_t>(prefix, kMaxIndexedWords);
+    uint8_t kind;
+    if (first_hash == pat.size() && pat.size() <= (size_t)kMaxIndexedWords) kind = kExact;
+    else if (first_hash < pat.size() && prefix <= (size_t)kMaxIndexedWords && first_hash + 1 == pat.size()) kind = kTail;
+    else kind = kComplex;
+    uint32_t mask = 0;
+    GroupBuild g;
+    for (size_t p = 0; p < ip; ++p)
+      if (pat[p] != kStar) { mask |= 1u << p; g.lits.push_back(pat[p]); }
+    if (kind == kComplex) { g.rem.assign(pat.begin() + ip, pat.end()); any_complex = true; }
+    auto sk = std::make_tuple(kind, (uint8_t)ip, mask);
+    auto sit = shape_ids.find(sk);
+    if (sit == shape_ids.end()) {
+      sit = shape_ids.emplace(sk, (uint32_t)shape_list.size()).first;
+      shape_list.push_back(sk);
+    }
+    g.shape_key = sit->second;
+    max_len = std::max<uint32_t>(max_len, (uint32_t)ip);
+    enc.clear();
+    enc.push_back(g.shape_key);
+    enc.insert(enc.end(), g.lits.begin(), g.lits.end());
+    enc.push_back(kNone);
+    enc.insert(enc.end(), g.rem.begin(), g.rem.end());
+    auto git = group_ids.find(enc);
+    if (git == group_ids.end()) {
+      git = group_ids.emplace(enc, (uint32_t)gb.size()).first;
+      gb.push_back(std::move(g));
+    }
+    GroupBuild& dst = gb[git->second];
+    dst.queues.push_back(qid.at(std::get<1>(t)));
+    dst.durable = dst.durable || std::get<2>(t);
+  }
+
+  // shapes: exact ones by length, then the '#' kinds by prefix length
+  std::vector<uint32_t> order(shape_list.size());
+  for (uint32_t i = 0; i < order.size(); ++i) order[i] = i;
+  auto rank_of = [&](uint32_t i) {
+    auto& s = shape_list[i];
+    return std::make_tuple(std::get<0>(s) == kExact ? 0 : 1, std::get<1>(s), std::get<0>(s), std::get<2>(s));
+  };
+  std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return rank_of(a) < rank_of(b); });
+  std::vector<uint32_t> new_shape(shape_list.size());
+  out.shapes.resize(shape_list.size());
+  for (uint32_t pos = 0; pos < order.size(); ++pos) {
+    auto& s = shape_list[order[pos]];
+    new_shape[order[pos]] = pos;
+    Shape sh{};
+    sh.kind = std::get<0>(s);
+    sh.len = std::get<1>(s);
+    sh.lit_mask = std::get<2>(s);
+    sh.seed = fin(mix(mix(0x243F6A8885A308D3ull, ((uint32_t)sh.kind << 8) | sh.len), sh.lit_mask));
+    out.shapes[pos] = sh;
+  }
+  {
+    uint32_t pos = 0;
+    for (int L = 0; L <= kLenCap; ++L) {
+      out.exact_rng[2 * L] = (uint16_t)pos;
+      while (pos < out.shapes.size() && out.shapes[pos].kind == kExact && out.shapes[pos].len == L) ++pos;
+      out.exact_rng[2 * L + 1] = (uint16_t)pos;
+    }
+    out.hashy_begin = pos;
+    out.hashy_end = (uint32_t)out.shapes.size();
+  }
+  out.wstride = any_complex ? (uint32_t)kMaxWords : std::max<uint32_t>(4, (max_len + 3) & ~3u);
+
+  // groups, literal tuples, remainders, queue lists; "shared" = some queue sits in two groups
+  std::vector<uint32_t> queue_uses(out.queue_names.size(), 0);
+  for (auto& g : gb) {
+    std::sort(g.queues.begin(), g.queues.end());
+    g.queues.erase(std::unique(g.queues.begin(), g.queues.end()), g.queues.end());
+    for (uint32_t q : g.queues) queue_uses[q]++;
+  }
+  out.groups.resize(gb.size());
+  // chain heads keyed by (shape, literal tuple); group_ids iterates in encoded order, so groups
+  // that differ only in their remainder are adjacent
+  std::map<std::vector<uint32_t>, uint32_t> heads;
+  std::vector<std::pair<uint64_t, uint32_t>> head_hash;  // (hash, head group)
+  for (uint32_t gi = 0; gi < gb.size(); ++gi) {
+    GroupBuild& g = gb[gi];
+    Group& d = out.groups[gi];
+    d = Group{};
+    d.shape = new_shape[g.shape_key];
+    d.list_off = (uint32_t)out.qlist.size();
+    d.list_len = (uint32_t)g.queues.size();
+    out.qlist.insert(out.qlist.end(), g.queues.begin(), g.queues.end());
+    d.lit_off = (uint32_t)out.lits.size();
+    d.nlit = (uint8_t)g.lits.size();
+    out.lits.insert(out.lits.end(), g.lits.begin(), g.lits.end());
+    d.rem_off = (uint32_t)out.rems.size();
+    d.rem_len = (uint16_t)g.rem.size();
+    out.rems.insert(out.rems.end(), g.rem.begin(), g.rem.end());
+    d.flags = g.durable ? kAnyDurable : 0;
+    for (uint32_t q : g.queues)
+      if (queue_uses[q] > 1) { d.flags |= kShared; break; }
+    d.next = kNone;
+    enc.clear();
+    enc.push_back(d.shape);
+    enc.insert(enc.end(), g.lits.begin(), g.lits.end());
+    auto hit = heads.find(enc);
+    if (hit == heads.end()) {
+      heads.emplace(enc, gi);
+      uint64_t h = out.shapes[d.shape].seed;
+      for (uint32_t l : g.lits) h = mix(h, l);
+      head_hash.emplace_back(fin(h), gi);
+    } else {
+      d.next = out.groups[hit->second].next;  // push behind the head
+      out.groups[hit->second].next = gi;
+    }
+  }
+  out.n_heads = head_hash.size();
+
+  // bucketed hash table: 4 slots per 32 B bucket, at most half full, linear probing by bucket;
+  // a bucket with an empty slot ends a probe sequence (no deletions: commit rebuilds)
+  uint32_t nb = pow2_at_least(std::max<uint64_t>(1, (head_hash.size() + 1) / 2));
+  out.slots.assign((size_t)nb * 4, Slot{0, 0});
+  for (auto& hh : head_hash) {
+    uint32_t b = (uint32_t)hh.first & (nb - 1);
+    for (;;) {
+      Slot* s = &out.slots[(size_t)b * 4];
+      int i = 0;
+      while (i < 4 && s[i].tag != 0) ++i;
+      if (i < 4) { s[i] = Slot{tag_of(hh.first), hh.second}; break; }
+      b = (b + 1) & (nb - 1);
+    }
+  }
+
+  // word dictionary (open addressing on the word hash, at most half full)
+  uint32_t nd = pow2_at_least(std::max<uint64_t>(2, words.size() * 2));
+  out.dict.assign(nd, DictSlot{});
+  for (auto& kv : words) {
+    DictSlot s{};
+    s.hash = word_hash(kv.first);
+    s.first8 = first8(kv.first);
+    s.len = (uint32_t)kv.first.size();
+    s.id = kv.second;
+    s.byte_off = (uint32_t)out.dict_bytes.size();
+    if (kv.first.size() > 8) out.dict_bytes.insert(out.dict_bytes.end(), kv.first.begin(), kv.first.end());
+    uint32_t i = (uint32_t)s.hash & (nd - 1);
+    while (out.dict[i].id != 0) i = (i + 1) & (nd - 1);
+    out.dict[i] = s;
+  }
+  if (out.dict_bytes.empty()) out.dict_bytes.push_back(0);
+}
+
+}  // namespace chq

@@ -1,0 +1,40 @@
+// Launch interface between the C-ABI layer and kernels.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "chq_common.h"
+
+namespace chq {
+
+constexpr int kRouteThreads = 256;   // messages per tile; one thread per message while probing
+constexpr int kRouteSlots = 8;       // matched groups remembered per message before the slow path
+constexpr int kRouteSmall = 512;     // ids (all lists but the longest) a warp merges in shared memory
+
+// control words (device): zeroed before every launch
+constexpr int kCtrlTile = 0, kCtrlStatus = 1, kCtrlScratchLo = 2 /* u64 bump pointer */, kCtrlWords = 4;
+constexpr uint32_t kStatusOverflow = 1, kStatusScratch = 2;
+
+struct RouteParams {
+  TableView tv;
+  const uint32_t* wid;       // [n][tv.wstride] interned words
+  const uint8_t* nwords;     // [n] word count after Java split (0 = error / nothing to route)
+  uint32_t n, n_tiles;
+  uint32_t* offsets;         // [n+1] out
+  uint32_t* ids;             // out
+  uint64_t ids_cap;
+  uint8_t* durable;          // [n] out
+  uint64_t* total;           // out: number of ids
+  uint64_t* tile_state;      // [n_tiles] scratch, zeroed before launch
+  uint32_t* ctrl;            // [kCtrlWords] scratch, zeroed before launch
+  uint32_t* scratch;         // slow-path arena
+  uint64_t scratch_cap;      // in ids
+  uint32_t max_slots, max_small;
+};
+
+cudaError_t launch_tokenize(const uint8_t* blob, const uint32_t* off, uint32_t n, const TableView& tv, int split,
+                            uint32_t* wid, uint8_t* nwords, uint8_t* err, cudaStream_t st);
+cudaError_t launch_route(const RouteParams& p, int n_sms, int32_t* d_status, cudaStream_t st);
+unsigned long long kernel_launches();
+
+}  // namespace chq

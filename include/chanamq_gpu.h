@@ -1,0 +1,125 @@
+/* libchanagpu.so — C ABI of the B200 routing path for ChanaMQ.
+ *
+ * The reference (Scala/Akka, no FFI of any kind) routes one message at a time through
+ *   trait QueueMatcher { subscribe; unsubscribe; lookup }          QueueMatcher.scala:11-27
+ * owned by one ExchangeEntity actor (ExchangeEntity.scala:126, chosen by exchange type at
+ * ExchangeEntity.scala:149-154 / 211-216).  This library sits behind that seam: a Scala
+ * `GpuMatcher extends QueueMatcher` binds the entry points below through JNA and
+ * hands a whole `Publishs` batch (ExchangeEntity.scala:293-308) to one chq_route call.
+ *
+ * Conventions: every function returns CHQ_OK (0) or a negative status; nothing throws or aborts
+ * across the boundary; caller buffers are only read during the call; results point into
+ * library-owned pinned memory that stays valid until the next route call on the same table.
+ * Calls on ONE table must be serialised by the caller (one exchange = one actor = one thread in
+ * the reference, ExchangeEntity.scala:107); different tables are independent.
+ *
+ * Paths relative to /root/reference/chana-mq-server/src/main/scala/chana/mq/amqp/server/.
+ */
+#ifndef CHANAMQ_GPU_H
+#define CHANAMQ_GPU_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct chq_table chq_table; /* one per exchange; opaque */
+
+/* AMQP.ExchangeType (chana-mq-base/.../model/AMQP.scala:33-46) */
+enum { CHQ_DIRECT = 0, CHQ_FANOUT = 1, CHQ_TOPIC = 2, CHQ_HEADERS = 3 };
+/* COMPAT = what the reference computes: '*' is one word, '#' is an ordinary word
+ *          (TrieMatcher.WILDCARD, engine/QueueMatcher.scala:70), headers routed as topic
+ *          (entity/ExchangeEntity.scala:153,215).
+ * SPEC   = AMQP 0-9-1 text: '#' is zero or more words. */
+enum { CHQ_MODE_COMPAT = 0, CHQ_MODE_SPEC = 1 };
+
+enum {
+  CHQ_OK = 0,
+  CHQ_E_ZERO_WORDS = -1,   /* "." / ".." : the reference throws ArrayIndexOutOfBounds (QueueMatcher.scala:420,528) */
+  CHQ_E_KEY_TOO_LONG = -2, /* more than 255 bytes: not an AMQP shortstr */
+  CHQ_E_OVERFLOW = -3,     /* result larger than the ids capacity given / than 2^32-1 ids */
+  CHQ_E_CUDA = -4,         /* CUDA failure; chq_last_error() has the text.  There is no CPU fallback. */
+  CHQ_E_ARG = -5,
+  CHQ_E_NOT_COMMITTED = -6,
+  CHQ_E_SCRATCH = -7       /* device scratch arena exhausted (device-level entry points only) */
+};
+
+const char* chq_last_error(void); /* thread-local text of the last failure */
+
+/* ---- table life cycle (ExchangeEntity Declare / load, entity/ExchangeEntity.scala:137-165, 211-216) ---- */
+/* device = CUDA ordinal.  device = -1 makes a host-only table: bind/commit/stats/queue names work (the
+ * compiler can be checked without a GPU) but every route call fails with CHQ_E_CUDA. */
+int32_t chq_table_create(chq_table** out, int32_t exchange_type, int32_t mode, int32_t device);
+int32_t chq_table_destroy(chq_table* t);
+
+/* QueueMatcher.subscribe as called from queueBind (entity/ExchangeEntity.scala:338):
+ * subscriber = TopicSubscriber(queue, isDurable) (entity/ExchangeEntity.scala:97).
+ * Binding an identical (key, queue, durable) triple again is a no-op (engine/QueueMatcher.scala:443-446). */
+int32_t chq_bind(chq_table* t, const uint8_t* key, uint32_t key_len, const uint8_t* queue, uint32_t queue_len,
+                 uint8_t durable);
+/* bulk form of the same call, for replaying the stored binds at start-up (entity/ExchangeEntity.scala:155-157) */
+int32_t chq_bind_many(chq_table* t, const uint8_t* keys_blob, const uint32_t* key_offsets,
+                      const uint8_t* queues_blob, const uint32_t* queue_offsets, const uint8_t* durable,
+                      uint32_t n);
+/* QueueMatcher.unsubscribe as called from queueUnbind(queue, routingKey) (entity/ExchangeEntity.scala:380).
+ * Clean set removal: the reference's tombstone defect is not reproduced. */
+int32_t chq_unbind(chq_table* t, const uint8_t* key, uint32_t key_len, const uint8_t* queue, uint32_t queue_len,
+                   uint8_t durable);
+/* queueUnbind(queue): drop every binding of a deleted queue (entity/ExchangeEntity.scala:344-351) */
+int32_t chq_unbind_queue(chq_table* t, const uint8_t* queue, uint32_t queue_len);
+/* Compile the binding set and upload it.  Queue ids are assigned here: the rank of the queue name
+ * among names that hold a binding, ascending by bytes, so ascending id = canonical order. */
+int32_t chq_commit(chq_table* t);
+int32_t chq_n_queues(const chq_table* t, uint32_t* n);
+int32_t chq_queue_name(const chq_table* t, uint32_t queue_id, const uint8_t** name, uint32_t* len);
+
+/* ---- batched lookup: the per-message body of ExchangeEntity.publish (entity/ExchangeEntity.scala:293-302)
+ *      for a whole Publishs batch.  Message i gets queue_ids[offsets[i] .. offsets[i+1]) — the SET of
+ *      queue names over all matching bindings (entity/ExchangeEntity.scala:300), ascending;
+ *      any_durable[i] = OR of the matched subscribers' isDurable (entity/ExchangeEntity.scala:302);
+ *      err[i] = 1 for a zero-word key, 2 for a key longer than 255 bytes (no queues then). ---- */
+typedef struct {
+  uint32_t n;
+  const uint32_t* offsets;   /* n+1 */
+  const uint32_t* queue_ids; /* offsets[n] */
+  const uint8_t* any_durable; /* n */
+  const uint8_t* err;        /* n */
+} chq_result;
+
+/* Host buffers in, host result out (H2D, kernels, D2H inside).  keys_blob / key_offsets may be
+ * ordinary or pinned host memory; pinned (chq_host_alloc) skips one staging copy.
+ * headers_blob / headers_offsets: raw AMQP field tables per message for CHQ_HEADERS in SPEC mode, else NULL. */
+int32_t chq_route(chq_table* t, const uint8_t* keys_blob, const uint32_t* key_offsets, uint32_t n,
+                  const uint8_t* headers_blob, const uint32_t* headers_offsets, chq_result* out);
+
+/* Pipelined form: up to CHQ_SLOTS batches in flight on one table (H2D of batch i+1 overlaps the
+ * kernels and D2H of batch i).  submit() returns at once; wait() blocks until that slot's result is
+ * on the host.  A slot's result stays valid until the slot is submitted again. */
+#define CHQ_SLOTS 4
+int32_t chq_route_submit(chq_table* t, int32_t slot, const uint8_t* keys_blob, const uint32_t* key_offsets,
+                         uint32_t n);
+int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out);
+
+/* Device buffers in, device result out, asynchronous on `stream` (a cudaStream_t; NULL = default
+ * stream).  d_status receives a chq status word once the stream reaches it; d_total the id count.
+ * d_ids holds ids_cap entries; a larger result sets CHQ_E_OVERFLOW and writes nothing past it. */
+int32_t chq_route_device(chq_table* t, const uint8_t* d_keys_blob, const uint32_t* d_key_offsets, uint32_t n,
+                         uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,
+                         uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream);
+
+/* pinned host memory for callers that want zero-copy staging (JNA: new Pointer(addr)) */
+int32_t chq_host_alloc(void** p, uint64_t bytes);
+int32_t chq_host_free(void* p);
+
+/* counters as a JSON object: bindings, queues, groups, shapes, word-id stride, batches, messages,
+ * ids, device bytes of the table */
+int32_t chq_stats(const chq_table* t, char* json, uint32_t cap);
+/* how many of this library's kernels have been launched by this process (all tables) */
+uint64_t chq_kernel_launches(void);
+/* test hook: lower the per-message limits that select the slower merge paths (0 = default) */
+int32_t chq_debug_limits(chq_table* t, uint32_t max_slots, uint32_t max_small);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -116,6 +116,17 @@ int orc_unbind(void* p, const uint8_t* key, uint32_t klen, const uint8_t* queue,
   return rc;
 }
 
+// bulk bind (blob + offsets form), same semantics as orc_bind per element; returns first error
+int orc_bind_many(void* p, const uint8_t* kb, const uint32_t* ko, const uint8_t* qb, const uint32_t* qo,
+                  const uint8_t* durable, uint32_t n) {
+  int first = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    int rc = orc_bind(p, kb + ko[i], ko[i + 1] - ko[i], qb + qo[i], qo[i + 1] - qo[i], durable ? durable[i] : 0);
+    if (rc && !first) first = rc;
+  }
+  return first;
+}
+
 uint32_t orc_n_queues(void* p) {
   auto* h = (Handle*)p;
   h->refresh();

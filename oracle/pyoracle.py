@@ -35,6 +35,8 @@ def lib():
         for f in (L.orc_bind, L.orc_unbind):
             f.restype = C.c_int
             f.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_int]
+        L.orc_bind_many.restype = C.c_int
+        L.orc_bind_many.argtypes = [C.c_void_p] * 6 + [C.c_uint32]
         L.orc_n_queues.restype = C.c_uint32
         L.orc_n_queues.argtypes = [C.c_void_p]
         L.orc_queue_name.restype = C.c_int
@@ -107,6 +109,10 @@ class Oracle:
     def unbind(self, key, queue, durable=False):
         k, q = _b(key), _b(queue)
         return self.L.orc_unbind(self.h, k, len(k), q, len(q), int(durable))
+
+    def bind_many(self, keys_blob, key_off, queues_blob, queue_off, durable):
+        a = [np.ascontiguousarray(x) for x in (keys_blob, key_off, queues_blob, queue_off, durable)]
+        return self.L.orc_bind_many(self.h, *[x.ctypes.data for x in a], len(key_off) - 1)
 
     def n_queues(self):
         return self.L.orc_n_queues(self.h)

@@ -1,0 +1,82 @@
+"""CPU-side checks of the product library (no compute calls: this container has no GPU): the C-ABI
+library loads and exports every symbol include/chanamq_gpu.h declares, the host-side table compiler
+behaves (host-only tables, device = -1), and the product refuses to route without CUDA — there is
+no CPU fallback."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from chanamq_b200 import CHQ_DIRECT, CHQ_FANOUT, CHQ_MODE_COMPAT, CHQ_MODE_SPEC, CHQ_TOPIC, ChqError, GpuMatcher
+from chanamq_b200 import _lib
+from chanamq_b200.workload import TopicWorkload, queue_names_packed
+from tests.test_oracle_kat import KAT_BINDS
+
+
+def test_library_exports_every_declared_symbol():
+    L = _lib.load_library()
+    declared = _lib.declared_symbols()
+    assert len(declared) >= 18
+    missing = [s for s in declared if not hasattr(L, s)]
+    assert missing == []
+
+
+def test_no_cpu_fallback():
+    m = GpuMatcher(CHQ_TOPIC, CHQ_MODE_COMPAT, device=-1)
+    m.bind("a.*", "q")
+    m.commit()
+    with pytest.raises(ChqError) as e:
+        m.lookup_all(["a.b"])
+    assert e.value.code == _lib.CHQ_E_CUDA
+
+
+def test_host_compile_of_the_reference_kat_table():
+    m = GpuMatcher(CHQ_TOPIC, CHQ_MODE_COMPAT, device=-1)
+    for k, q in KAT_BINDS:
+        m.bind(k, q)
+    m.bind("forex.*", "s0")  # identical pair again: no-op (QueueMatcher.scala:443-446)
+    st = m.stats()
+    assert st["bindings"] == 8 and st["queues"] == 4 and st["groups"] == 7 and st["shapes"] == 5
+    assert m.queue_names() == [b"s0", b"s1", b"s2", b"tmp_541b184c-6213-487c-a254-f1a8e3d461ab"]
+    assert m.try_bind(".", "x") == _lib.CHQ_E_ZERO_WORDS and m.try_bind("..", "x") == _lib.CHQ_E_ZERO_WORDS
+    assert m.try_bind("k" * 256, "x") == _lib.CHQ_E_KEY_TOO_LONG
+    m.unbind_queue("s0")
+    assert m.stats()["bindings"] == 5 and b"s0" not in m.queue_names()
+
+
+def test_shapes_and_word_stride():
+    m = GpuMatcher(CHQ_TOPIC, CHQ_MODE_SPEC, device=-1)
+    for k in ["a.b.c", "a.*.c", "*.b.c", "a.b.#", "a.#", "x.y.z.w.v.u"]:
+        m.bind(k, "q")
+    st = m.stats()
+    assert st["shapes"] == 6 and st["wstride"] == 8
+    m.bind("a.#.b", "q")           # '#' in the middle: remainder verified by the NFA, all words kept
+    assert m.stats()["wstride"] == 128
+    c = GpuMatcher(CHQ_TOPIC, CHQ_MODE_COMPAT, device=-1)
+    c.bind("a.#.b", "q")           # COMPAT: '#' is a word (QueueMatcher.scala:70)
+    assert c.stats()["wstride"] == 4 and c.stats()["shapes"] == 1
+    d = GpuMatcher(CHQ_DIRECT, device=-1)
+    d.bind(".", "q"); d.bind("a.b.c.d.e.f.g.h.i", "q")
+    assert d.stats()["wstride"] == 4 and d.stats()["words"] == 2
+    f = GpuMatcher(CHQ_FANOUT, device=-1)
+    f.bind("x", "q1"); f.bind("y", "q2")
+    assert f.stats()["groups"] == 1
+
+
+def test_generator_is_deterministic_and_compiles_at_scale():
+    w1, w2 = TopicWorkload(2), TopicWorkload(2)
+    b1, o1 = w1.keys(5000, stream=3)
+    b2, o2 = w2.keys(5000, stream=3)
+    assert np.array_equal(b1, b2) and np.array_equal(o1, o2)
+    b3, _ = w1.keys(5000, stream=4)
+    assert not np.array_equal(b1[:1000], b3[:1000])
+    pb, poff, q, d = w1.patterns(50_000, 12_500, hash_tail=True)
+    assert q.max() == 12_499 and set(np.unique(d)) == {0, 1}
+    qb, qoff = queue_names_packed(q)
+    assert bytes(qb[:8]) == b"q0000000" and bytes(qb[-8:]) == b"q%07d" % q[-1]
+    m = GpuMatcher(CHQ_TOPIC, CHQ_MODE_SPEC, device=-1)
+    m.bind_many(pb, poff, qb, qoff, d)
+    m.commit()
+    st = m.stats()
+    assert st["queues"] == 12_500 and 40_000 < st["groups"] <= st["bindings"] <= 50_000
+    assert st["shapes"] < 120 and st["wstride"] == 8
