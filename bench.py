@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""Benchmark of the routing hot path: routed msgs/sec, topic exchange, 1 M bindings (BASELINE.json).
+
+One "step" = one batch of 2^20 synthetic routing keys routed against the 1 M-binding table
+(tokenise + fused route kernel).  Ten distinct batches (10.5 M keys, the "10 M messages" of
+BASELINE.json configs[3]) stay resident in HBM and rotate, so no step re-reads what the previous one
+left in L2, and every step writes ~0.4 GB of queue ids (> the 126 MB L2).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]          product arm (CUDA, C ABI)
+  python bench.py --impl reference ...                         the reference's CPU routing (C++ restatement
+                                                               of TrieMatcher: no JVM in this image), all host threads
+
+Multi-GPU (torchrun, one rank per GPU): the path shards by KEYS — every rank holds the whole compiled
+table (tens of MB) and routes its own batches; there is no data-path collective, so scaling is weak
+(per-GPU work fixed).  The binding-slice mode of BASELINE.json configs[3] is a separate code path
+(chanamq_b200.sharded) and is not what this line times.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "routed msgs/sec (topic, 1M bindings)"
+UNIT = "msgs/s"
+SEED = 4            # T(seed=4, P=1 000 000, N=10 000 000)
+N_BATCHES = 10
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bindings", type=int, default=1_000_000)
+    ap.add_argument("--batch", type=int, default=1 << 20)
+    ap.add_argument("--mode", default="compat", choices=["compat", "spec"],
+                    help="compat = the reference's semantics ('#' is a word); spec = AMQP '#' wildcard")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample", type=int, default=100_000)
+    ap.add_argument("--ref-sample", type=int, default=0, help="keys per reference-arm step (0 = 12 500 x threads)")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return ("topic exchange, %d bindings with mixed */# patterns (T(seed=%d), one queue per binding), %s semantics, "
+            "batches of %d keys x %d resident batches" % (
+                a.bindings, SEED, "reference (COMPAT: '#' literal)" if a.mode == "compat" else "AMQP (SPEC: '#' wildcard)",
+                a.batch, N_BATCHES))
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line)
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_table_inputs(a):
+    from chanamq_b200.workload import TopicWorkload, queue_names_packed
+
+    w = TopicWorkload(SEED)
+    pb, poff, q, d = w.patterns(a.bindings, a.bindings, hash_tail=True)
+    qb, qoff = queue_names_packed(q)
+    return w, (pb, poff, qb, qoff, d)
+
+
+# --------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the C++ restatement of the reference's TrieMatcher (oracle/)
+# --------------------------------------------------------------------------------------------
+def cpu_route_rate(a, w, binds, n_keys, threads, steps, warmup, stream0=1000):
+    from oracle import pyoracle as po
+
+    o = po.Oracle(po.TOPIC, po.COMPAT if a.mode == "compat" else po.SPEC, inplace=True)
+    t0 = time.perf_counter()
+    assert o.bind_many(*binds) == 0
+    build_s = time.perf_counter() - t0
+    secs, ids = [], 0
+    for s in range(warmup + steps):
+        blob, off = w.keys(n_keys, stream=stream0 + s)
+        t0 = time.perf_counter()
+        o_off, o_ids, _, _ = o.route_packed(blob, off, threads)
+        dt = time.perf_counter() - t0   # lookups + collapsing to the CSR the exchange consumes
+        if s >= warmup:
+            secs.append(dt)
+            ids += len(o_ids)
+    return n_keys * steps / sum(secs), sum(secs) / steps, build_s, ids / max(1, n_keys * steps)
+
+
+def run_reference(a, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n_keys = a.ref_sample or 12_500 * threads
+    w, binds = make_table_inputs(a)
+    rate, per_step, build_s, mbar = cpu_route_rate(a, w, binds, n_keys, threads, a.steps, a.warmup)
+    sample = "%d keys per step x %d steps on %d threads (keys sharded over a read-only trie); trie build %.1f s not timed" % (
+        n_keys, a.steps, threads, build_s)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "mean_queues_per_message": mbar},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "C++ restatement of the reference's TrieMatcher + ExchangeEntity dedup (oracle/); the Scala itself "
+                "cannot run here (no JVM) and is expected to be slower (GC, boxing)",
+    }))
+
+
+# --------------------------------------------------------------------------------------------
+# product arm
+# --------------------------------------------------------------------------------------------
+def run_ours(a, rank, world, local_rank):
+    import torch
+
+    from chanamq_b200 import CHQ_MODE_COMPAT, CHQ_MODE_SPEC, CHQ_TOPIC, GpuMatcher
+    from chanamq_b200._lib import load_library
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=dev)
+
+    L = load_library()
+    w, binds = make_table_inputs(a)
+    t0 = time.perf_counter()
+    m = GpuMatcher(CHQ_TOPIC, CHQ_MODE_COMPAT if a.mode == "compat" else CHQ_MODE_SPEC, device=local_rank)
+    m.bind_many(*binds)
+    m.commit()
+    build_s = time.perf_counter() - t0
+    st = m.stats()
+
+    # ---- inputs: N_BATCHES distinct batches per rank, in pinned host memory and resident in HBM ----
+    n = a.batch
+    host, devb = [], []
+    words_total = 0
+    for b in range(N_BATCHES):
+        blob, off = w.keys(n, stream=rank * 1000 + b)
+        hb = torch.empty(len(blob), dtype=torch.uint8).pin_memory()
+        ho = torch.empty(n + 1, dtype=torch.int32).pin_memory()
+        hb.numpy()[:] = blob
+        ho.numpy()[:] = off.view(np.int32)
+        host.append((hb, ho))
+        devb.append((hb.to(dev), ho.to(dev)))
+        words_total += int(np.count_nonzero(blob == ord("."))) + n
+    wbar = words_total / (N_BATCHES * n)
+
+    # ---- device-resident arm -------------------------------------------------------------------
+    ids_cap = int(n * 160)
+    d_offsets = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    d_ids = torch.empty(ids_cap, dtype=torch.int32, device=dev)
+    d_dur = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_err = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_tot = torch.zeros(2 * N_BATCHES, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step_device(i):
+        b = i % N_BATCHES
+        db, do = devb[b]
+        m.route_device(db.data_ptr(), do.data_ptr(), n, d_offsets.data_ptr(), d_ids.data_ptr(), ids_cap,
+                       d_dur.data_ptr(), d_err.data_ptr(), d_tot.data_ptr() + 16 * b, d_tot.data_ptr() + 16 * b + 8, stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(a.warmup):
+        step_device(i)
+    barrier()
+    m.profile(True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = L.chq_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(a.steps):
+        step_device(a.warmup + i)
+    e1.record()
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    launches = L.chq_kernel_launches() - launches0
+    tok_ms, route_ms, prof_n = m.profile(False)
+    clocks = sampler.stop()
+    tot = d_tot.cpu().numpy().reshape(N_BATCHES, 2)
+    used = sorted({(a.warmup + i) % N_BATCHES for i in range(a.steps)} | {i % N_BATCHES for i in range(a.warmup)})
+    if any((int(tot[b, 1]) & 0xFFFFFFFF) != 0 for b in used):
+        raise SystemExit("bench.py: route status %s" % [int(tot[b, 1]) & 0xFFFFFFFF for b in used])
+    ids_per_batch = float(np.mean([tot[b, 0] for b in used]))
+    mbar = ids_per_batch / n
+
+    # ---- end to end through the host-buffer C-ABI call (pinned inputs, H2D + kernels + D2H) -----
+    depth = 3
+
+    def e2e_run(steps, base):
+        inflight = []
+        chk = 0
+        for i in range(steps):
+            slot = i % depth
+            if len(inflight) == depth:
+                r = m.wait(inflight.pop(0))
+                chk += int(r.offsets[-1])
+            hb, ho = host[(base + i) % N_BATCHES]
+            m.submit(slot, hb.data_ptr(), ho.data_ptr(), n)
+            inflight.append(slot)
+        for s in inflight:
+            r = m.wait(s)
+            chk += int(r.offsets[-1])
+        return chk
+
+    e2e_run(min(a.warmup, depth) + depth, 0)
+    barrier()
+    t0 = time.perf_counter()
+    chk = e2e_run(a.steps, a.warmup)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    h2d = int(np.mean([hb.numel() + ho.numel() * 4 for hb, ho in host]))
+    d2h = int((n + 1) * 4 + 2 * n + 16 + ids_per_batch * 4)
+
+    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if dist:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    value = world * n * a.steps / (dev_ms * 1e-3)
+    e2e_value = world * n * a.steps / (e2e_ms * 1e-3)
+
+    if rank == 0:
+        peaks, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+        try:
+            peaks = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+            peak_src = "MEASURED_PEAKS.json hbm_gbs"
+        except Exception:
+            pass
+        wp = st["pattern_words"] / max(1, st["bindings"])
+        # B_topic = N(4 W + 4 + 4 M + 4) + P(4 Wp + 8), per k_route launch
+        alg_bytes = n * (4 * wbar + 4 + 4 * mbar + 4) + st["bindings"] * (4 * wp + 8)
+        route_ms_avg = route_ms / max(1, prof_n)
+        achieved = alg_bytes / (route_ms_avg * 1e-3) / 1e9
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "route_traffic.json")))["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": dev_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "mean_words_per_key": wbar, "mean_queues_per_message": mbar,
+                       "sharding": "keys (table replicated per GPU, no data-path collective)",
+                       "l2": "10 distinct resident batches rotate; each step writes ~%.0f MB of ids (> 126 MB L2)" % (ids_per_batch * 4 / 1e6),
+                       "table": {k: st[k] for k in ("bindings", "queues", "groups", "shapes", "words", "wstride", "table_bytes")},
+                       "table_build_s": build_s},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms / a.steps, "pipeline_depth": depth, "checksum_ids": chk,
+                    "timing": "host wall clock around K pipelined chq_route_submit/chq_route_wait calls, pinned host keys in, host CSR out"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks, "unit": "GB/s", "frac": achieved / peaks,
+                         "traffic": traffic, "kernel": "k_route", "kernel_ms": route_ms_avg,
+                         "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                         "tokenize_ms": tok_ms / max(1, prof_n), "kernel_share_of_step": route_ms / dev_ms if world == 1 else None},
+        }
+        if world == 1 and not a.no_cpu_baseline:
+            rate, per_step, cbuild, cm = cpu_route_rate(a, w, binds, a.cpu_sample, 1, 1, 0, stream0=0)
+            out["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
+                                   "sample": "%d keys of batch 0 on 1 thread (one exchange = one actor = one thread in the "
+                                             "reference, ExchangeEntity.scala:107), %.1f s; trie build %.1f s not timed; "
+                                             "C++ restatement of TrieMatcher (no JVM here)" % (a.cpu_sample, per_step, cbuild)}
+        print(json.dumps(out))
+    if dist:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    libs = [os.path.join(ROOT, "chanamq_b200", "libchanagpu.so"), os.path.join(ROOT, "chanamq_b200", "libchqgen.so"),
+            os.path.join(ROOT, "oracle", "liboracle.so")]
+    if not all(os.path.exists(p) for p in libs):  # normally prebuilt in-tree by __graft_entry__.build()
+        if rank == 0:
+            import __graft_entry__ as ge
+
+            ge.build()
+        else:
+            while not all(os.path.exists(p) for p in libs):
+                time.sleep(0.5)
+            time.sleep(1.0)
+    if a.impl == "reference":
+        run_reference(a, rank)
+        return
+    run_ours(a, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

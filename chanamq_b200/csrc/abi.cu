@@ -83,7 +83,15 @@ struct Workspace {
   DevBuf<uint64_t> state;   // [0..1] = control words, [2..] = per-tile scan state
   DevBuf<uint32_t> scratch;
   size_t scratch_want = 16u << 20;
-  void release() { wid.release(); nwords.release(); state.release(); scratch.release(); }
+  // optional per-kernel timing (chq_profile): events on the launching stream around each kernel
+  static constexpr int kProfRing = 256;
+  cudaEvent_t ev[kProfRing][3] = {};
+  int prof_n = 0;
+  void release() {
+    wid.release(); nwords.release(); state.release(); scratch.release();
+    for (auto& e : ev) for (auto& x : e) if (x) { cudaEventDestroy(x); x = nullptr; }
+    prof_n = 0;
+  }
 };
 
 struct RouteSlot {
@@ -132,6 +140,7 @@ struct chq_table {
   RouteSlot slots[CHQ_SLOTS];
   Workspace dev_ws;  // for chq_route_device
   uint32_t max_slots = kRouteSlots, max_small = kRouteSmall;
+  bool profile = false;
   uint64_t n_batches = 0, n_messages = 0, n_ids = 0;
   std::mutex mu;  // bind may arrive from a Future callback off the actor thread (ExchangeEntity.scala:337-338)
   chq_table(int type, int mode) : host(type, mode) {}
@@ -197,7 +206,15 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
     return CHQ_OK;
   }
   const int split = (t->host.type() == CHQ_TOPIC || t->host.type() == CHQ_HEADERS) ? 1 : 0;
+  cudaEvent_t* pe = nullptr;
+  if (t->profile && ws.prof_n < Workspace::kProfRing) {
+    pe = ws.ev[ws.prof_n++];
+    for (int i = 0; i < 3; ++i)
+      if (!pe[i]) CU(cudaEventCreate(&pe[i]));
+    CU(cudaEventRecord(pe[0], st));
+  }
   CU(launch_tokenize(d_blob, d_off, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
+  if (pe) CU(cudaEventRecord(pe[1], st));
   RouteParams p{};
   p.tv = t->tv;
   p.wid = ws.wid.p;
@@ -215,7 +232,9 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   p.scratch_cap = ws.scratch.cap;
   p.max_slots = t->max_slots;
   p.max_small = t->max_small;
-  CU(launch_route(p, t->n_sms, d_status, st));
+  CU(launch_route(p, t->n_sms, st));
+  if (pe) CU(cudaEventRecord(pe[2], st));
+  CU(launch_finish(p.ctrl, d_status, st));
   t->n_batches++;
   t->n_messages += n;
   return CHQ_OK;
@@ -491,6 +510,35 @@ int32_t chq_stats(const chq_table* t, char* json, uint32_t cap) {
                    (unsigned long long)table_bytes, (unsigned long long)t->n_batches, (unsigned long long)t->n_messages,
                    (unsigned long long)t->n_ids, t->compiled ? "true" : "false");
   return (w < 0 || (uint32_t)w >= cap) ? fail(CHQ_E_ARG, "chq_stats: buffer too small") : CHQ_OK;
+}
+
+int32_t chq_profile(chq_table* t, int32_t enable, double* tokenize_ms, double* route_ms, uint32_t* launches) {
+  if (!t) return fail(CHQ_E_ARG, "chq_profile: bad argument");
+  if (t->host_only) return fail(CHQ_E_CUDA, "chq_profile: host-only table");
+  int rc = set_device(t);
+  if (rc) return rc;
+  CU(cudaDeviceSynchronize());
+  double tk = 0, rt = 0;
+  uint32_t cnt = 0;
+  Workspace* all[CHQ_SLOTS + 1];
+  for (int i = 0; i < CHQ_SLOTS; ++i) all[i] = &t->slots[i].ws;
+  all[CHQ_SLOTS] = &t->dev_ws;
+  for (Workspace* ws : all) {
+    for (int i = 0; i < ws->prof_n; ++i) {
+      float a = 0, b = 0;
+      CU(cudaEventElapsedTime(&a, ws->ev[i][0], ws->ev[i][1]));
+      CU(cudaEventElapsedTime(&b, ws->ev[i][1], ws->ev[i][2]));
+      tk += a;
+      rt += b;
+      ++cnt;
+    }
+    ws->prof_n = 0;
+  }
+  if (tokenize_ms) *tokenize_ms = tk;
+  if (route_ms) *route_ms = rt;
+  if (launches) *launches = cnt;
+  t->profile = enable != 0;
+  return CHQ_OK;
 }
 
 uint64_t chq_kernel_launches(void) { return kernel_launches() ; }

@@ -567,7 +567,13 @@ __global__ void k_finish(const uint32_t* ctrl, int32_t* status) {
   *status = (s & kStatusScratch) ? CHQ_E_SCRATCH : (s & kStatusOverflow) ? CHQ_E_OVERFLOW : CHQ_OK;
 }
 
-cudaError_t launch_route(const RouteParams& p, int n_sms, int32_t* d_status, cudaStream_t st) {
+cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t st) {
+  k_finish<<<1, 1, 0, st>>>(ctrl, d_status);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st) {
   if (p.n_tiles == 0) return cudaSuccess;
   static int occ = 0;
   if (occ == 0) {
@@ -578,8 +584,7 @@ cudaError_t launch_route(const RouteParams& p, int n_sms, int32_t* d_status, cud
   const uint64_t want = (uint64_t)n_sms * occ;
   const uint32_t grid = (uint32_t)(p.n_tiles < want ? p.n_tiles : want);
   k_route<<<grid, kRouteThreads, 0, st>>>(p);
-  k_finish<<<1, 1, 0, st>>>(p.ctrl, d_status);
-  g_launches += 2;
+  ++g_launches;
   return cudaGetLastError();
 }
 

@@ -152,6 +152,12 @@ class GpuMatcher:
         check(self.L.chq_stats(self.h, buf, 2048))
         return json.loads(buf.value.decode())
 
+    def profile(self, enable):
+        """-> (tokenize_ms, route_ms, batches) summed since the last call; then switch recording on/off"""
+        a, b, n = C.c_double(), C.c_double(), C.c_uint32()
+        check(self.L.chq_profile(self.h, int(enable), C.byref(a), C.byref(b), C.byref(n)))
+        return a.value, b.value, n.value
+
     def debug_limits(self, max_slots=0, max_small=0):
         check(self.L.chq_debug_limits(self.h, max_slots, max_small))
 

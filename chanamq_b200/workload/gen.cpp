@@ -4,7 +4,7 @@
 // V = [32, 1024, 16384, 64, 64, 64] sampled Zipf(s) with s = [1.0, 0.5, 0.0, 0.5, 0.5, 0.5],
 // words of 3-8 lowercase letters.  Binding patterns are made from independently sampled keys:
 // 70 % exact, 25 % one '*', 5 % two '*'; with `hash_tail` a further 10 % get their suffix after
-// word j >= 2 replaced by a single '#'.  Nothing here comes from the reference (it ships no
+// word j >= 2 replaced by a single '#' (their first two words are kept literal).  Nothing here comes from the reference (it ships no
 // generator; its perf specs drive an external tool, chana-mq-test/perf/test.sh:2).
 #include <algorithm>
 #include <cmath>
@@ -134,6 +134,10 @@ uint64_t chqgen_topic_patterns(void* gp, uint32_t p, uint32_t n_queues, int hash
       int j = 2 + (int)r.below(d - 2);  // keep words 0..j-1, then '#'
       kind[j] = 2;
       d = j + 1;
+      // the first two words of a '#' pattern stay literal: "*.*.#" would match every key and
+      // 1 M bindings of that mixture would emit thousands of queues per message (the degenerate
+      // shape SURVEY.md §8(d) warns about)
+      kind[0] = kind[1] = 0;
     }
     pos += emit(g, idx, kind, d, blob + pos);
     queue[i] = i % n_queues;

@@ -114,6 +114,10 @@ int32_t chq_host_free(void* p);
 /* counters as a JSON object: bindings, queues, groups, shapes, word-id stride, batches, messages,
  * ids, device bytes of the table */
 int32_t chq_stats(const chq_table* t, char* json, uint32_t cap);
+/* Per-kernel device time, measured with CUDA events recorded on the launching stream around k_tokenize
+ * and k_route.  The call synchronises the device, returns the sums (ms) and the number of batches since
+ * the last call (at most 256 are kept), then switches recording on or off. */
+int32_t chq_profile(chq_table* t, int32_t enable, double* tokenize_ms, double* route_ms, uint32_t* launches);
 /* how many of this library's kernels have been launched by this process (all tables) */
 uint64_t chq_kernel_launches(void);
 /* test hook: lower the per-message limits that select the slower merge paths (0 = default) */
