@@ -102,6 +102,15 @@ CHQ_HD uint64_t fin(uint64_t h) {
   return h;
 }
 CHQ_HD uint32_t tag_of(uint64_t h) { return (uint32_t)(h >> 32) | 1u; }
+// Zobrist-style tuple hash: hash(shape, literal tuple) = shape.seed ^ XOR over literal positions p
+// of zob(p, word id at p).  A key computes zob() once per word and every shape it is probed under
+// costs only a few XORs.
+CHQ_HD uint64_t zob(uint32_t p, uint32_t w) {
+  uint64_t x = ((uint64_t)(p + 1) << 32 | w) * 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
 // FNV-1a over the word's bytes, one byte at a time so the tokeniser can fold it into its scan
 constexpr uint64_t kFnvBasis = 0xCBF29CE484222325ull;
 constexpr uint64_t kFnvPrime = 0x100000001B3ull;

@@ -270,8 +270,10 @@ void HostTable::compile(CompiledTable& out) const {
     if (hit == heads.end()) {
       heads.emplace(enc, gi);
       uint64_t h = out.shapes[d.shape].seed;
-      for (uint32_t l : g.lits) h = mix(h, l);
-      head_hash.emplace_back(fin(h), gi);
+      uint32_t li = 0;
+      for (uint32_t mk = out.shapes[d.shape].lit_mask; mk; mk &= mk - 1, ++li)
+        h ^= zob((uint32_t)__builtin_ctz(mk), g.lits[li]);
+      head_hash.emplace_back(h, gi);
     } else {
       d.next = out.groups[hit->second].next;  // push behind the head
       out.groups[hit->second].next = gi;

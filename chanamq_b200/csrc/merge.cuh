@@ -1,0 +1,278 @@
+// Warp-level set union of sorted queue-id lists (included by kernels.cu only).
+//
+// A routed message matched k >= 1 groups; each group owns a sorted, duplicate-free list of queue
+// ids in the (L2-resident) table.  The result the exchange needs is the sorted union
+// (ExchangeEntity.scala:300 collapses subscribers to a SET of queue names).  Typical shape: one
+// long list ("a.*.*" bound by hundreds of queues) and a few short ones.  So: the short lists are
+// staged in shared memory and rank-merged there; the long list is streamed from L2 in chunks of
+// 32 and the short ids are woven in with shuffle-based mutual ranks — no per-element serial work,
+// no atomics, coalesced stores.
+#pragma once
+#include "kernels.h"
+#include "probe.cuh"
+
+namespace chq {
+namespace {
+
+struct WarpScratch {
+  uint32_t a[kRouteSmall];   // staged short lists, back to back
+  uint32_t b[kRouteSmall];   // their sorted union
+  uint32_t st[kRouteSlots];  // start of list j inside a[]
+  uint32_t ln[kRouteSlots];  // its length (0 for the long list)
+};
+
+__device__ __forceinline__ uint32_t smem_lower_bound(const uint32_t* a, uint32_t n, uint32_t x) {
+  uint32_t lo = 0;
+  while (n) {
+    const uint32_t half = n >> 1;
+    if (a[lo + half] < x) { lo += half + 1; n -= half + 1; }
+    else n = half;
+  }
+  return lo;
+}
+__device__ __forceinline__ uint32_t smem_upper_bound(const uint32_t* a, uint32_t n, uint32_t x) {
+  uint32_t lo = 0;
+  while (n) {
+    const uint32_t half = n >> 1;
+    if (a[lo + half] <= x) { lo += half + 1; n -= half + 1; }
+    else n = half;
+  }
+  return lo;
+}
+
+__device__ void warp_bitonic_sort(uint32_t* a, uint32_t np, int lane) {
+  for (uint32_t size = 2; size <= np; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t t = lane; t < (np >> 1); t += 32) {
+        const uint32_t i = ((t / stride) * (stride << 1)) + (t % stride), j = i + stride;
+        const bool up = (i & size) == 0;
+        const uint32_t x = a[i], y = a[j];
+        if ((x > y) == up) { a[i] = y; a[j] = x; }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// In-place removal of adjacent duplicates of a sorted array by one warp; returns the new length.
+__device__ uint32_t warp_unique(uint32_t* a, uint32_t n, int lane) {
+  uint32_t kept = 0;
+  for (uint32_t base = 0; base < n; base += 32) {
+    const uint32_t i = base + lane;
+    const uint32_t v = i < n ? a[i] : 0;
+    const bool keep = i < n && (i == 0 || a[i - 1] != v);
+    __syncwarp();
+    const unsigned m = __ballot_sync(kFull, keep);
+    if (keep) a[kept + __popc(m & ((1u << lane) - 1))] = v;
+    kept += __popc(m);
+    __syncwarp();
+  }
+  return kept;
+}
+
+// number of the 32 lane values `v` (ascending across lanes, padded with kNone) that are < x: 0..32
+__device__ __forceinline__ uint32_t lanes_below(uint32_t v, uint32_t x) {
+  uint32_t q = 0;
+#pragma unroll
+  for (int step = 16; step; step >>= 1) {
+    const uint32_t probe = __shfl_sync(kFull, v, q + step - 1);
+    if (probe < x) q += step;
+  }
+  const uint32_t last = __shfl_sync(kFull, v, q);
+  return q + (last < x ? 1u : 0u);
+}
+
+// Fast path of warp_union: the short lists hold at most 32 ids together (the usual case: one long
+// list plus a few one- or two-id lists).  The short ids live in one register per lane, are sorted
+// with shuffles, and are woven into the streamed long list one id at a time.
+//   short_len / short_st: per lane j < k, length of list j (0 for the long one) and its start
+//   among the short ids.
+template <bool WRITE>
+__device__ uint32_t warp_union_small(const uint32_t* __restrict__ qlist, uint32_t my_off, uint32_t short_len,
+                                     uint32_t short_st, int k, bool dedup, uint32_t big_off, uint32_t nb, uint32_t ns,
+                                     uint32_t* __restrict__ out, uint64_t pos, uint64_t cap, int lane) {
+  uint32_t s = kNone;
+  const unsigned short_lanes = __ballot_sync(kFull, short_len > 0);
+  const int n_short = __popc(short_lanes);
+  if (n_short == 2) {
+    // two sorted lists: one ascending from lane 0, the other descending from lane 31 -> bitonic merge
+    const int j1 = __ffs(short_lanes) - 1, j2 = 31 - __clz(short_lanes);
+    const uint32_t o1 = __shfl_sync(kFull, my_off, j1), l1 = __shfl_sync(kFull, short_len, j1);
+    const uint32_t o2 = __shfl_sync(kFull, my_off, j2), l2 = __shfl_sync(kFull, short_len, j2);
+    if ((uint32_t)lane < l1) s = __ldg(qlist + o1 + lane);
+    else if ((uint32_t)lane >= 32 - l2) s = __ldg(qlist + o2 + (31 - lane));
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+      const uint32_t other = __shfl_xor_sync(kFull, s, d);
+      s = (lane & d) == 0 ? min(s, other) : max(s, other);
+    }
+  } else {
+    for (unsigned todo = short_lanes; todo; todo &= todo - 1) {
+      const int j = __ffs(todo) - 1;
+      const uint32_t o = __shfl_sync(kFull, my_off, j), l = __shfl_sync(kFull, short_len, j);
+      const uint32_t st = __shfl_sync(kFull, short_st, j);
+      if ((uint32_t)lane >= st && (uint32_t)lane < st + l) s = __ldg(qlist + o + (lane - st));
+    }
+    if (n_short > 2) {
+#pragma unroll
+      for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (int d = size >> 1; d; d >>= 1) {
+          const uint32_t other = __shfl_xor_sync(kFull, s, d);
+          const bool up = (lane & size) == 0, lower = (lane & d) == 0;
+          s = (lower == up) ? min(s, other) : max(s, other);
+        }
+      }
+    }
+  }
+  // an id present in two short lists is emitted once
+  const uint32_t prev = __shfl_up_sync(kFull, s, 1);
+  const int sdup = (dedup && lane > 0 && s == prev) ? 1 : 0;
+
+  uint32_t t = 0, kept_total = 0;
+  uint32_t b_next = (uint32_t)lane < nb ? __ldg(qlist + big_off + lane) : kNone;
+  for (uint32_t c0 = 0; c0 < nb; c0 += 32) {
+    const uint32_t i = c0 + lane;
+    const bool valid = i < nb;
+    const uint32_t b = b_next;
+    b_next = (i + 32 < nb) ? __ldg(qlist + big_off + i + 32) : kNone;
+    const uint32_t bmax = __shfl_sync(kFull, b, min(31u, nb - c0 - 1));
+    const uint32_t kept0 = kept_total;
+    uint32_t shift = 0;
+    while (t < ns) {
+      const uint32_t st = __shfl_sync(kFull, s, t);
+      if (st > bmax) break;
+      const int skip = __shfl_sync(kFull, sdup, t);
+      const unsigned lt = __ballot_sync(kFull, valid && b < st);
+      const unsigned eq = __ballot_sync(kFull, valid && b == st);
+      if (!skip && eq == 0) {
+        const uint32_t p = __popc(lt);
+        if (WRITE && lane == 0) {
+          const uint64_t o = pos + c0 + p + kept_total;
+          if (o < cap) out[o] = st;
+        }
+        if ((uint32_t)lane >= p) ++shift;
+        ++kept_total;
+      }
+      ++t;
+    }
+    if (WRITE && valid) {
+      const uint64_t o = pos + i + kept0 + shift;
+      if (o < cap) out[o] = b;
+    }
+  }
+  // short ids above the whole long list
+  const bool tail = (uint32_t)lane >= t && (uint32_t)lane < ns && !sdup;
+  const unsigned tm = __ballot_sync(kFull, tail);
+  if (WRITE && tail) {
+    const uint64_t o = pos + nb + kept_total + __popc(tm & ((1u << lane) - 1));
+    if (o < cap) out[o] = s;
+  }
+  return nb + kept_total + __popc(tm);
+}
+
+// Lane j < k holds list j = qlist[my_off .. my_off + my_len).  Precondition: the lists other than
+// the longest hold at most kRouteSmall ids together.  `dedup` = some id may sit in two lists.
+// Returns the size of the union; with WRITE the union goes to out[pos ...), never past cap.
+template <bool WRITE>
+__device__ uint32_t warp_union(const uint32_t* __restrict__ qlist, uint32_t my_off, uint32_t my_len, int k, bool dedup,
+                               WarpScratch& ws, uint32_t* __restrict__ out, uint64_t pos, uint64_t cap, int lane) {
+  // the longest list is streamed; everything else is "short"
+  const uint32_t len_k = lane < k ? my_len : 0;
+  uint32_t nb = len_k;
+#pragma unroll
+  for (int d = 16; d; d >>= 1) nb = max(nb, __shfl_xor_sync(kFull, nb, d));
+  const int big = __ffs(__ballot_sync(kFull, lane < k && len_k == nb)) - 1;
+  const uint32_t big_off = __shfl_sync(kFull, my_off, big);
+  const uint32_t short_len = (lane < k && lane != big) ? my_len : 0;
+  uint32_t incl = short_len;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t v = __shfl_up_sync(kFull, incl, d);
+    if (lane >= d) incl += v;
+  }
+  uint32_t ns = __shfl_sync(kFull, incl, 31);
+  if (ns <= 32)  // the common case: a handful of short ids — keep them in registers
+    return warp_union_small<WRITE>(qlist, my_off, short_len, incl - short_len, k, dedup, big_off, nb, ns, out, pos, cap, lane);
+  if (lane < k) { ws.st[lane] = incl - short_len; ws.ln[lane] = short_len; }
+  for (int j = 0; j < k; ++j) {
+    const uint32_t o = __shfl_sync(kFull, my_off, j), l = __shfl_sync(kFull, short_len, j);
+    const uint32_t st = __shfl_sync(kFull, incl - short_len, j);
+    for (uint32_t i = lane; i < l; i += 32) ws.a[st + i] = __ldg(qlist + o + i);
+  }
+  __syncwarp();
+  const uint32_t* S = ws.a;
+  if (k > 2) {
+    // rank-merge: every id finds its place among the other short lists by binary search
+    for (uint32_t e = lane; e < ns; e += 32) {
+      int j = 0;
+      while (e >= ws.st[j] + ws.ln[j]) ++j;
+      const uint32_t x = ws.a[e];
+      uint32_t r = e - ws.st[j];
+      for (int j2 = 0; j2 < k; ++j2) {
+        const uint32_t l2 = ws.ln[j2];
+        if (j2 == j || l2 == 0) continue;
+        r += j2 < j ? smem_upper_bound(ws.a + ws.st[j2], l2, x) : smem_lower_bound(ws.a + ws.st[j2], l2, x);
+      }
+      ws.b[r] = x;
+    }
+    __syncwarp();
+    if (dedup) ns = warp_unique(ws.b, ns, lane);
+    S = ws.b;
+  }
+  // weave the short ids into the long list, 32 x 32 at a time
+  uint32_t t = 0, kept_total = 0;
+  uint32_t b_next = lane < nb ? __ldg(qlist + big_off + lane) : kNone;
+  for (uint32_t c0 = 0; c0 < nb; c0 += 32) {
+    const uint32_t i = c0 + lane;
+    const bool valid = i < nb;
+    const uint32_t b = b_next;
+    b_next = (i + 32 < nb) ? __ldg(qlist + big_off + i + 32) : kNone;
+    const uint32_t bmax = __shfl_sync(kFull, b, min(31u, nb - c0 - 1));
+    const uint32_t kept0 = kept_total;
+    uint32_t shift = 0;
+    while (t < ns) {
+      const uint32_t s = (t + lane < ns) ? S[t + lane] : kNone;
+      const bool inr = s <= bmax;  // in-range lanes form a prefix (S ascending; ids < kNone)
+      const unsigned m_in = __ballot_sync(kFull, inr);
+      if (m_in == 0) break;
+      // p = how many ids of this chunk are < s  (s <= bmax, so p <= 31)
+      uint32_t p = 0;
+#pragma unroll
+      for (int step = 16; step; step >>= 1) {
+        const uint32_t probe = __shfl_sync(kFull, b, p + step - 1);
+        if (probe < s) p += step;
+      }
+      const bool dup = __shfl_sync(kFull, b, p) == s;
+      const bool keep = inr && !dup;
+      const unsigned km = __ballot_sync(kFull, keep);
+      if (WRITE && keep) {
+        const uint64_t o = pos + c0 + p + kept_total + __popc(km & ((1u << lane) - 1));
+        if (o < cap) out[o] = s;
+      }
+      // every long id moves up by the kept short ids below it
+      const uint32_t q = lanes_below(inr ? s : kNone, b);
+      shift += __popc(km & (q >= 32 ? kFull : ((1u << q) - 1)));
+      kept_total += __popc(km);
+      const uint32_t n_in = __popc(m_in);
+      t += n_in;
+      if (n_in < 32) break;
+    }
+    if (WRITE && valid) {
+      const uint64_t o = pos + i + kept0 + shift;
+      if (o < cap) out[o] = b;
+    }
+  }
+  // short ids above the whole long list
+  if (WRITE) {
+    for (uint32_t i = t + lane; i < ns; i += 32) {
+      const uint64_t o = pos + nb + kept_total + (i - t);
+      if (o < cap) out[o] = S[i];
+    }
+  }
+  __syncwarp();
+  return nb + kept_total + (ns - t);
+}
+
+}  // namespace
+}  // namespace chq
