@@ -102,15 +102,17 @@ CHQ_HD uint64_t fin(uint64_t h) {
   return h;
 }
 CHQ_HD uint32_t tag_of(uint64_t h) { return (uint32_t)(h >> 32) | 1u; }
-// Zobrist-style tuple hash: hash(shape, literal tuple) = shape.seed ^ XOR over literal positions p
-// of zob(p, word id at p).  A key computes zob() once per word and every shape it is probed under
-// costs only a few XORs.
-CHQ_HD uint64_t zob(uint32_t p, uint32_t w) {
-  uint64_t x = ((uint64_t)(p + 1) << 32 | w) * 0x9E3779B97F4A7C15ull;
-  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
-  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
-  return x ^ (x >> 31);
+// Zobrist-style tuple hash (32 bit): hash(shape, literal tuple) = shape seed ^ XOR over the literal
+// positions p of zob(p, word id at p).  A key computes zob() once per word, and every shape it is
+// probed under then costs a few XORs.  The low bits pick the bucket, the whole value (|1) is the
+// slot tag; a tag hit is always confirmed against the stored tuple, so the hash only has to be fast.
+CHQ_HD uint32_t zob(uint32_t p, uint32_t w) {
+  uint32_t x = w ^ ((p + 1) * 0x9E3779B9u);
+  x ^= x >> 16; x *= 0x85EBCA6Bu;
+  x ^= x >> 13; x *= 0xC2B2AE35u;
+  return x ^ (x >> 16);
 }
+CHQ_HD uint32_t tag32(uint32_t h) { return h | 1u; }
 // FNV-1a over the word's bytes, one byte at a time so the tokeniser can fold it into its scan
 constexpr uint64_t kFnvBasis = 0xCBF29CE484222325ull;
 constexpr uint64_t kFnvPrime = 0x100000001B3ull;

@@ -244,7 +244,7 @@ void HostTable::compile(CompiledTable& out) const {
   // chain heads keyed by (shape, literal tuple); group_ids iterates in encoded order, so groups
   // that differ only in their remainder are adjacent
   std::map<std::vector<uint32_t>, uint32_t> heads;
-  std::vector<std::pair<uint64_t, uint32_t>> head_hash;  // (hash, head group)
+  std::vector<std::pair<uint32_t, uint32_t>> head_hash;  // (hash, head group)
   for (uint32_t gi = 0; gi < gb.size(); ++gi) {
     GroupBuild& g = gb[gi];
     Group& d = out.groups[gi];
@@ -269,7 +269,7 @@ void HostTable::compile(CompiledTable& out) const {
     auto hit = heads.find(enc);
     if (hit == heads.end()) {
       heads.emplace(enc, gi);
-      uint64_t h = out.shapes[d.shape].seed;
+      uint32_t h = (uint32_t)out.shapes[d.shape].seed;
       uint32_t li = 0;
       for (uint32_t mk = out.shapes[d.shape].lit_mask; mk; mk &= mk - 1, ++li)
         h ^= zob((uint32_t)__builtin_ctz(mk), g.lits[li]);
@@ -286,12 +286,12 @@ void HostTable::compile(CompiledTable& out) const {
   uint32_t nb = pow2_at_least(std::max<uint64_t>(1, (head_hash.size() + 1) / 2));
   out.slots.assign((size_t)nb * 4, Slot{0, 0});
   for (auto& hh : head_hash) {
-    uint32_t b = (uint32_t)hh.first & (nb - 1);
+    uint32_t b = hh.first & (nb - 1);
     for (;;) {
       Slot* s = &out.slots[(size_t)b * 4];
       int i = 0;
       while (i < 4 && s[i].tag != 0) ++i;
-      if (i < 4) { s[i] = Slot{tag_of(hh.first), hh.second}; break; }
+      if (i < 4) { s[i] = Slot{tag32(hh.first), hh.second}; break; }
       b = (b + 1) & (nb - 1);
     }
   }

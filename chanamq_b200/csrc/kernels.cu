@@ -316,16 +316,19 @@ __global__ void __launch_bounds__(kRouteThreads, 4) k_route(RouteParams p) {
       const uint32_t kc = sm.kcls[t];
       const int kk = kc & 0xFF, cl = (kc >> 8) & 0xF;
       const uint64_t o = sm.pos[t];
+      if (o + c > p.ids_cap) continue;  // does not fit: the launch reports CHQ_E_OVERFLOW; nothing is written past ids_cap
       if (cl == 2) {
         const uint64_t so = ((uint64_t)sm.llen[0][t] << 32) | sm.loff[0][t];
-        for (uint32_t i = lane; i < c; i += 32)
-          if (o + i < p.ids_cap) p.ids[o + i] = p.scratch[so + i];
+        for (uint32_t i = lane; i < c; i += 32) p.ids[o + i] = p.scratch[so + i];
       } else if (kk == 1) {
-        const uint32_t lo = sm.loff[0][t];
-        const uint32_t* src = tv.qlist + lo;
-#pragma unroll 4
-        for (uint32_t i = lane; i < c; i += 32)
-          if (o + i < p.ids_cap) p.ids[o + i] = __ldg(src + i);
+        const uint32_t* src = tv.qlist + sm.loff[0][t] + lane;
+        uint32_t* dst = p.ids + o + lane;
+        uint32_t i = lane;
+        for (; i + 96 < c; i += 128, src += 128, dst += 128) {
+          const uint32_t v0 = __ldg(src), v1 = __ldg(src + 32), v2 = __ldg(src + 64), v3 = __ldg(src + 96);
+          dst[0] = v0; dst[32] = v1; dst[64] = v2; dst[96] = v3;
+        }
+        for (; i < c; i += 32, src += 32, dst += 32) *dst = __ldg(src);
       } else {
         uint32_t lo = 0, ll = 0;
         if (lane < kk) { lo = sm.loff[lane][t]; ll = sm.llen[lane][t]; }

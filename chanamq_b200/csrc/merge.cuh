@@ -129,45 +129,46 @@ __device__ uint32_t warp_union_small(const uint32_t* __restrict__ qlist, uint32_
   const uint32_t prev = __shfl_up_sync(kFull, s, 1);
   const int sdup = (dedup && lane > 0 && s == prev) ? 1 : 0;
 
+  // Stream the long list.  `dst` walks the output with the chunk; lanes past the end of the list
+  // hold kNone, so in the last chunk every remaining short id is "in range" and lands after it.
+  (void)cap;
   uint32_t t = 0, kept_total = 0;
-  uint32_t b_next = (uint32_t)lane < nb ? __ldg(qlist + big_off + lane) : kNone;
-  for (uint32_t c0 = 0; c0 < nb; c0 += 32) {
-    const uint32_t i = c0 + lane;
-    const bool valid = i < nb;
+  uint32_t s_next = __shfl_sync(kFull, s, 0);  // ns >= 1
+  const uint32_t* src = qlist + big_off + lane;
+  uint32_t* dst = WRITE ? out + pos + lane : nullptr;
+  uint32_t b_next = (uint32_t)lane < nb ? __ldg(src) : kNone;
+  for (uint32_t left = nb; left > 0; left = left > 32 ? left - 32 : 0) {
     const uint32_t b = b_next;
-    b_next = (i + 32 < nb) ? __ldg(qlist + big_off + i + 32) : kNone;
-    const uint32_t bmax = __shfl_sync(kFull, b, min(31u, nb - c0 - 1));
-    const uint32_t kept0 = kept_total;
+    src += 32;
+    b_next = ((uint32_t)lane + 32 < left) ? __ldg(src) : kNone;
+    const uint32_t bmax = __shfl_sync(kFull, b, 31);
     uint32_t shift = 0;
-    while (t < ns) {
-      const uint32_t st = __shfl_sync(kFull, s, t);
-      if (st > bmax) break;
-      const int skip = __shfl_sync(kFull, sdup, t);
-      const unsigned lt = __ballot_sync(kFull, valid && b < st);
-      const unsigned eq = __ballot_sync(kFull, valid && b == st);
-      if (!skip && eq == 0) {
-        const uint32_t p = __popc(lt);
-        if (WRITE && lane == 0) {
-          const uint64_t o = pos + c0 + p + kept_total;
-          if (o < cap) out[o] = st;
+    if (t < ns && s_next <= bmax) {
+      const uint32_t kept0 = kept_total;
+      do {
+        const int skip = __shfl_sync(kFull, sdup, t);
+        const unsigned lt = __ballot_sync(kFull, b < s_next);
+        const unsigned eq = __ballot_sync(kFull, b == s_next);
+        if (!skip && eq == 0) {
+          const uint32_t p = __popc(lt);
+          if (WRITE && lane == 0) dst[p + kept_total] = s_next;
+          if ((uint32_t)lane >= p) ++shift;
+          ++kept_total;
         }
-        if ((uint32_t)lane >= p) ++shift;
-        ++kept_total;
-      }
-      ++t;
+        ++t;
+        s_next = t < ns ? __shfl_sync(kFull, s, t) : kNone;
+      } while (s_next <= bmax && t < ns);
+      shift += kept0;
+    } else {
+      shift = kept_total;
     }
-    if (WRITE && valid) {
-      const uint64_t o = pos + i + kept0 + shift;
-      if (o < cap) out[o] = b;
-    }
+    if (WRITE && (uint32_t)lane < left) dst[shift] = b;
+    if (WRITE) dst += 32;
   }
-  // short ids above the whole long list
+  // short ids that are larger than a FULL last chunk's maximum (nb a multiple of 32)
   const bool tail = (uint32_t)lane >= t && (uint32_t)lane < ns && !sdup;
   const unsigned tm = __ballot_sync(kFull, tail);
-  if (WRITE && tail) {
-    const uint64_t o = pos + nb + kept_total + __popc(tm & ((1u << lane) - 1));
-    if (o < cap) out[o] = s;
-  }
+  if (WRITE && tail) out[pos + nb + kept_total + __popc(tm & ((1u << lane) - 1))] = s;
   return nb + kept_total + __popc(tm);
 }
 

@@ -69,7 +69,7 @@ __device__ __forceinline__ Shape load_shape(const TableView& tv, uint32_t s) {
 // What one key needs for all of its probes, computed once: the Zobrist term of each of its first
 // eight words (two 128-bit loads of the word-id row) and which of them no binding mentions.
 struct KeyCtx {
-  uint64_t z[8];
+  uint32_t z[8];
   const uint32_t* row;
   uint32_t nw;
   uint32_t unknown;   // bit p: word p is kUnknownWord (can only meet a wildcard)
@@ -98,7 +98,7 @@ __device__ __forceinline__ void key_ctx_init(KeyCtx& k, const uint32_t* __restri
 // literal positions, or kNone.  Exact: on a tag hit the stored tuple is compared word by word.
 __device__ __forceinline__ uint32_t probe_head(const TableView& tv, uint32_t shape_idx, const Shape& sh, const KeyCtx& k) {
   if (sh.lit_mask & k.unknown & 0xFFu) return kNone;
-  uint64_t h = sh.seed;
+  uint32_t h = (uint32_t)sh.seed;
 #pragma unroll
   for (int p = 0; p < 8; ++p)
     if ((sh.lit_mask >> p) & 1u) h ^= k.z[p];
@@ -108,8 +108,8 @@ __device__ __forceinline__ uint32_t probe_head(const TableView& tv, uint32_t sha
     if (w == kUnknownWord) return kNone;
     h ^= zob(p, w);
   }
-  const uint32_t tag = tag_of(h);
-  uint32_t b = (uint32_t)h & tv.bucket_mask;
+  const uint32_t tag = tag32(h);
+  uint32_t b = h & tv.bucket_mask;
   for (;;) {
     const uint4 s01 = ldg16(&tv.slots[(size_t)b * 4]);
     const uint4 s23 = ldg16(&tv.slots[(size_t)b * 4 + 2]);

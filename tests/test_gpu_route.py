@@ -234,4 +234,5 @@ def test_device_entry_point_with_torch_buffers():
                    d_dur.data_ptr(), d_err.data_ptr(), d_tot.data_ptr(), d_tot.data_ptr() + 8, st)
     torch.cuda.synchronize()
     assert (int(d_tot[1].item()) & 0xFFFFFFFF) == (-3 & 0xFFFFFFFF) and int(d_ids2[1000].item()) == -7
-    assert np.array_equal(d_ids2[:1000].cpu().numpy().view(np.uint32), o_ids[:1000])
+    fit = int(o_off[o_off <= 1000].max())  # messages that fit entirely are still written
+    assert fit > 0 and np.array_equal(d_ids2[:fit].cpu().numpy().view(np.uint32), o_ids[:fit])
