@@ -28,6 +28,7 @@ def build_product(force=False, verbose=False):
         return out
     cmd = [NVCC, *ARCH, "-O3", "-std=c++17", "-lineinfo", "-shared", "-Xcompiler", "-fPIC,-Wall",
            "-cudart", "static", "-o", out, *srcs]
+    cmd[1:1] = os.environ.get("CHQ_NVCC_DEFS", "").split()  # experiment switches, e.g. -DCHQ_PROBE_BATCH=2
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     subprocess.check_call(cmd)

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -133,7 +134,8 @@ struct chq_table {
   DevBuf<uint8_t> d_dict_bytes;
   DevBuf<Shape> d_shapes;
   DevBuf<uint16_t> d_exact;
-  DevBuf<Slot> d_slots;
+  DevBuf<uint16_t> d_tags;
+  DevBuf<uint32_t> d_slot_group;
   DevBuf<Group> d_groups;
   DevBuf<uint32_t> d_lits, d_rems, d_qlist;
   TableView tv{};
@@ -161,7 +163,8 @@ int upload_table(chq_table* t) {
   if ((rc = t->d_dict_bytes.upload(c.dict_bytes.data(), c.dict_bytes.size(), st))) return rc;
   if ((rc = t->d_shapes.upload(c.shapes.data(), c.shapes.size(), st))) return rc;
   if ((rc = t->d_exact.upload(c.exact_rng.data(), c.exact_rng.size(), st))) return rc;
-  if ((rc = t->d_slots.upload(c.slots.data(), c.slots.size(), st))) return rc;
+  if ((rc = t->d_tags.upload(c.tags.data(), c.tags.size(), st))) return rc;
+  if ((rc = t->d_slot_group.upload(c.slot_group.data(), c.slot_group.size(), st))) return rc;
   if ((rc = t->d_groups.upload(c.groups.data(), c.groups.size(), st))) return rc;
   if ((rc = t->d_lits.upload(c.lits.data(), c.lits.size(), st))) return rc;
   if ((rc = t->d_rems.upload(c.rems.data(), c.rems.size(), st))) return rc;
@@ -175,8 +178,9 @@ int upload_table(chq_table* t) {
   v.exact_rng = t->d_exact.p;
   v.hashy_begin = c.hashy_begin;
   v.hashy_end = c.hashy_end;
-  v.slots = t->d_slots.p;
-  v.bucket_mask = (uint32_t)(c.slots.size() / 4) - 1;
+  v.tags = t->d_tags.p;
+  v.slot_group = t->d_slot_group.p;
+  v.bucket_mask = (uint32_t)(c.tags.size() / kBucketSlots) - 1;
   v.groups = t->d_groups.p;
   v.lits = t->d_lits.p;
   v.rems = t->d_rems.p;
@@ -232,6 +236,7 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   p.scratch_cap = ws.scratch.cap;
   p.max_slots = t->max_slots;
   p.max_small = t->max_small;
+  { const char* dbg = getenv("CHQ_DEBUG"); p.debug = dbg ? (uint32_t)atoi(dbg) : 0u; }
   CU(launch_route(p, t->n_sms, st));
   if (pe) CU(cudaEventRecord(pe[2], st));
   CU(launch_finish(p.ctrl, d_status, st));
@@ -308,7 +313,7 @@ int32_t chq_table_destroy(chq_table* t) {
   for (auto& s : t->slots) s.release();
   t->dev_ws.release();
   t->d_dict.release(); t->d_dict_bytes.release(); t->d_shapes.release(); t->d_exact.release();
-  t->d_slots.release(); t->d_groups.release(); t->d_lits.release(); t->d_rems.release(); t->d_qlist.release();
+  t->d_tags.release(); t->d_slot_group.release(); t->d_groups.release(); t->d_lits.release(); t->d_rems.release(); t->d_qlist.release();
   delete t;
   return CHQ_OK;
 }
@@ -499,7 +504,7 @@ int32_t chq_stats(const chq_table* t, char* json, uint32_t cap) {
   if (!t || !json || !cap) return fail(CHQ_E_ARG, "chq_stats: bad argument");
   const CompiledTable& c = t->ct;
   const uint64_t table_bytes = c.dict.size() * sizeof(DictSlot) + c.dict_bytes.size() + c.shapes.size() * sizeof(Shape) +
-                               c.slots.size() * sizeof(Slot) + c.groups.size() * sizeof(Group) +
+                               c.tags.size() * 2 + c.slot_group.size() * 4 + c.groups.size() * sizeof(Group) +
                                (c.lits.size() + c.rems.size() + c.qlist.size()) * 4;
   int w = snprintf(json, cap,
                    "{\"bindings\": %llu, \"queues\": %zu, \"groups\": %zu, \"heads\": %llu, \"shapes\": %zu, "

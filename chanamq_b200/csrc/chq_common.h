@@ -41,23 +41,33 @@ struct Shape {            // 16 B
   uint16_t pad;
 };
 
-enum GroupFlags : uint8_t { kAnyDurable = 1, kShared = 2 };
+enum GroupFlags : uint8_t {
+  kAnyDurable = 1,   // some binding's queue is durable (ExchangeEntity.scala:302)
+  kShared = 2,       // some queue here is also bound through another group (union must de-duplicate)
+  kHasRem = 4,       // a remainder has to be run through the word-level NFA
+};
 
-struct Group {            // 32 B, one L2 sector
+struct Group {            // 64 B; the first 32 B sector answers most probe hits on its own
   uint32_t list_off;      // into qlist: sorted unique queue ids bound with exactly this pattern
   uint32_t list_len;
-  uint32_t lit_off;       // into lits: the literal word ids, in position order
   uint32_t next;          // next group with the same (shape, literal tuple) but another remainder
-  uint32_t rem_off;       // into rems: pattern words after the indexed prefix (kComplex)
-  uint16_t rem_len;
+  uint16_t shape;
   uint8_t nlit;
-  uint8_t flags;          // kAnyDurable: some binding's queue is durable (ExchangeEntity.scala:302)
-                          // kShared: some queue here is also bound through another group
-  uint32_t shape;
+  uint8_t flags;          // GroupFlags
+  // zpos[p] = zob(p, literal word id at prefix position p) for p < 8, 0 where the shape has a '*'.
+  // zob(p, .) is a bijection on 32 bits, so comparing it with the key's zob(p, word) IS comparing
+  // the words — the key keeps those values in registers, which makes verification load-free.
+  uint32_t zpos[8];
+  uint32_t rem_off;       // into rems: pattern words after the indexed prefix (kHasRem)
+  uint32_t rem_len;
+  uint32_t lit_off;       // into lits: all literal word ids in position order (literals at positions >= 8)
   uint32_t pad;
 };
 
-struct Slot { uint32_t tag; uint32_t group; };   // 4 slots = one 32 B bucket; tag 0 = empty
+// Hash index over the chain heads: buckets of eight slots.  tags[] holds one 16-bit tag per slot
+// (0 = empty), so a probe is ONE 16-byte load; slot_group[] names the head group of a slot and is
+// only read on a tag hit.  Built at most ~3/8 full; a bucket with an empty slot ends a probe.
+constexpr int kBucketSlots = 8;
 
 struct DictSlot {         // 32 B: one interned pattern word
   uint64_t hash;
@@ -74,9 +84,12 @@ struct TableView {
   const uint8_t* dict_bytes;
   uint32_t dict_mask;
   const Shape* shapes;
-  const uint16_t* exact_rng;   // [2*(kLenCap+1)]: shapes of kind kExact with len == L are [rng[2L], rng[2L+1])
-  uint32_t hashy_begin, hashy_end;   // kTail/kComplex shapes, ascending len
-  const Slot* slots;
+  // [3*(kLenCap+1)]: for a key of L words, rng[3L], rng[3L+1] = the kExact shapes with len == L,
+  // and [hashy_begin, rng[3L+2]) = the kTail/kComplex shapes (ascending len) with len <= L
+  const uint16_t* exact_rng;
+  uint32_t hashy_begin, hashy_end;
+  const uint16_t* tags;        // [buckets * 8] 16-bit tags; a bucket is one aligned 16-byte load
+  const uint32_t* slot_group;  // [buckets * 8]
   uint32_t bucket_mask;
   const Group* groups;
   const uint32_t* lits;
@@ -104,15 +117,15 @@ CHQ_HD uint64_t fin(uint64_t h) {
 CHQ_HD uint32_t tag_of(uint64_t h) { return (uint32_t)(h >> 32) | 1u; }
 // Zobrist-style tuple hash (32 bit): hash(shape, literal tuple) = shape seed ^ XOR over the literal
 // positions p of zob(p, word id at p).  A key computes zob() once per word, and every shape it is
-// probed under then costs a few XORs.  The low bits pick the bucket, the whole value (|1) is the
-// slot tag; a tag hit is always confirmed against the stored tuple, so the hash only has to be fast.
+// probed under then costs a few XORs.  The low bits pick the bucket, tag16() the slot tag; a tag
+// hit is always confirmed against the stored tuple, so the hash only has to be fast.
 CHQ_HD uint32_t zob(uint32_t p, uint32_t w) {
   uint32_t x = w ^ ((p + 1) * 0x9E3779B9u);
   x ^= x >> 16; x *= 0x85EBCA6Bu;
   x ^= x >> 13; x *= 0xC2B2AE35u;
   return x ^ (x >> 16);
 }
-CHQ_HD uint32_t tag32(uint32_t h) { return h | 1u; }
+CHQ_HD uint32_t tag16(uint32_t h) { return ((h * 0x9E3779B1u) >> 16) | 1u; }
 // FNV-1a over the word's bytes, one byte at a time so the tokeniser can fold it into its scan
 constexpr uint64_t kFnvBasis = 0xCBF29CE484222325ull;
 constexpr uint64_t kFnvPrime = 0x100000001B3ull;

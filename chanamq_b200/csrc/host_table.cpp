@@ -90,7 +90,7 @@ struct GroupBuild {
 void HostTable::compile(CompiledTable& out) const {
   out = CompiledTable();
   out.n_bindings = live_.size();
-  out.exact_rng.assign(2 * (kLenCap + 1), 0);
+  out.exact_rng.assign(3 * (kLenCap + 1), 0);
 
   // queue ids: rank of the name among the names that hold a binding, ascending by bytes
   {
@@ -107,7 +107,8 @@ void HostTable::compile(CompiledTable& out) const {
 
   if (type_ == CHQ_FANOUT) {  // FanoutMatcher.lookup: every subscriber (QueueMatcher.scala:63-65)
     out.dict.assign(1, DictSlot{});
-    out.slots.assign(4, Slot{0, 0});
+    out.tags.assign(kBucketSlots, 0);
+    out.slot_group.assign(kBucketSlots, kNone);
     if (!live_.empty()) {
       Group g{};
       g.next = kNone;
@@ -224,12 +225,17 @@ void HostTable::compile(CompiledTable& out) const {
   {
     uint32_t pos = 0;
     for (int L = 0; L <= kLenCap; ++L) {
-      out.exact_rng[2 * L] = (uint16_t)pos;
+      out.exact_rng[3 * L] = (uint16_t)pos;
       while (pos < out.shapes.size() && out.shapes[pos].kind == kExact && out.shapes[pos].len == L) ++pos;
-      out.exact_rng[2 * L + 1] = (uint16_t)pos;
+      out.exact_rng[3 * L + 1] = (uint16_t)pos;
     }
     out.hashy_begin = pos;
     out.hashy_end = (uint32_t)out.shapes.size();
+    for (int L = 0; L <= kLenCap; ++L) {  // '#' shapes whose prefix fits in a key of L words
+      uint32_t e = out.hashy_begin;
+      while (e < out.hashy_end && out.shapes[e].len <= L) ++e;
+      out.exact_rng[3 * L + 2] = (uint16_t)e;
+    }
   }
   out.wstride = any_complex ? (uint32_t)kMaxWords : std::max<uint32_t>(4, (max_len + 3) & ~3u);
 
@@ -249,7 +255,7 @@ void HostTable::compile(CompiledTable& out) const {
     GroupBuild& g = gb[gi];
     Group& d = out.groups[gi];
     d = Group{};
-    d.shape = new_shape[g.shape_key];
+    d.shape = (uint16_t)new_shape[g.shape_key];
     d.list_off = (uint32_t)out.qlist.size();
     d.list_len = (uint32_t)g.queues.size();
     out.qlist.insert(out.qlist.end(), g.queues.begin(), g.queues.end());
@@ -257,9 +263,16 @@ void HostTable::compile(CompiledTable& out) const {
     d.nlit = (uint8_t)g.lits.size();
     out.lits.insert(out.lits.end(), g.lits.begin(), g.lits.end());
     d.rem_off = (uint32_t)out.rems.size();
-    d.rem_len = (uint16_t)g.rem.size();
+    d.rem_len = (uint32_t)g.rem.size();
+    {
+      uint32_t li = 0;
+      for (uint32_t mk = out.shapes[d.shape].lit_mask; mk; mk &= mk - 1, ++li) {
+        const uint32_t pos = (uint32_t)__builtin_ctz(mk);
+        if (pos < 8) d.zpos[pos] = zob(pos, g.lits[li]);
+      }
+    }
     out.rems.insert(out.rems.end(), g.rem.begin(), g.rem.end());
-    d.flags = g.durable ? kAnyDurable : 0;
+    d.flags = (g.durable ? kAnyDurable : 0) | (g.rem.empty() ? 0 : kHasRem);
     for (uint32_t q : g.queues)
       if (queue_uses[q] > 1) { d.flags |= kShared; break; }
     d.next = kNone;
@@ -281,17 +294,22 @@ void HostTable::compile(CompiledTable& out) const {
   }
   out.n_heads = head_hash.size();
 
-  // bucketed hash table: 4 slots per 32 B bucket, at most half full, linear probing by bucket;
-  // a bucket with an empty slot ends a probe sequence (no deletions: commit rebuilds)
-  uint32_t nb = pow2_at_least(std::max<uint64_t>(1, (head_hash.size() + 1) / 2));
-  out.slots.assign((size_t)nb * 4, Slot{0, 0});
+  // hash index over the chain heads: eight 16-bit tags per bucket, about 3/8 full, linear probing
+  // by bucket; a bucket with an empty slot ends a probe sequence (no deletions: commit rebuilds)
+  uint32_t nb = pow2_at_least(std::max<uint64_t>(1, (head_hash.size() + 2) / 3));
+  out.tags.assign((size_t)nb * kBucketSlots, 0);
+  out.slot_group.assign((size_t)nb * kBucketSlots, kNone);
   for (auto& hh : head_hash) {
     uint32_t b = hh.first & (nb - 1);
     for (;;) {
-      Slot* s = &out.slots[(size_t)b * 4];
+      uint16_t* t = &out.tags[(size_t)b * kBucketSlots];
       int i = 0;
-      while (i < 4 && s[i].tag != 0) ++i;
-      if (i < 4) { s[i] = Slot{tag32(hh.first), hh.second}; break; }
+      while (i < kBucketSlots && t[i] != 0) ++i;
+      if (i < kBucketSlots) {
+        t[i] = (uint16_t)tag16(hh.first);
+        out.slot_group[(size_t)b * kBucketSlots + i] = hh.second;
+        break;
+      }
       b = (b + 1) & (nb - 1);
     }
   }

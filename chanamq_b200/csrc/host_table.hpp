@@ -22,7 +22,8 @@ struct CompiledTable {
   std::vector<Shape> shapes;
   std::vector<uint16_t> exact_rng;
   uint32_t hashy_begin = 0, hashy_end = 0;
-  std::vector<Slot> slots;
+  std::vector<uint16_t> tags;          // [buckets * 8]
+  std::vector<uint32_t> slot_group;    // [buckets * 8]
   std::vector<Group> groups;
   std::vector<uint32_t> lits, rems, qlist;
   uint32_t wstride = 4;

@@ -22,6 +22,10 @@
 #include "merge.cuh"
 #include "probe.cuh"
 
+#ifndef CHQ_MIN_CTAS
+#define CHQ_MIN_CTAS 6
+#endif
+
 namespace chq {
 
 // One thread per key.  Java split semantics: words are cut at every '.', trailing
@@ -69,6 +73,8 @@ constexpr int kWarps = kRouteThreads / 32;
 struct RouteSmem {
   uint32_t loff[kRouteSlots][kRouteThreads];  // per message: matched lists (offset, length), slot-major
   uint32_t llen[kRouteSlots][kRouteThreads];
+  uint32_t cslot[kRouteSlots][kRouteThreads];  // probe pass: tag hits still to be resolved (slot, shape)
+  uint32_t cshape[kRouteSlots][kRouteThreads]; // shape << 16 | literal mask
   uint64_t pos[kRouteThreads];                // final CSR position of the message's ids
   uint32_t cnt[kRouteThreads];
   uint16_t kcls[kRouteThreads];               // k | class << 8 | dedup << 12
@@ -85,8 +91,10 @@ __device__ uint32_t warp_fallback(const RouteParams& p, const uint32_t* __restri
                                   uint64_t* scr_off, uint32_t* any_flags) {
   const TableView& tv = p.tv;
   const bool fan = tv.exchange_type == 1;
-  const uint32_t e0 = nw <= (uint32_t)kLenCap ? tv.exact_rng[2 * nw] : 0, e1 = nw <= (uint32_t)kLenCap ? tv.exact_rng[2 * nw + 1] : 0;
-  const uint32_t n_exact = e1 - e0, n_shapes = fan ? 0 : n_exact + (tv.hashy_end - tv.hashy_begin);
+  const uint32_t L = min(nw, (uint32_t)kLenCap);
+  const uint32_t e0 = nw <= (uint32_t)kLenCap ? tv.exact_rng[3 * L] : 0;
+  const uint32_t n_exact = nw <= (uint32_t)kLenCap ? tv.exact_rng[3 * L + 1] - e0 : 0;
+  const uint32_t n_shapes = fan ? 0 : n_exact + (tv.exact_rng[3 * L + 2] - tv.hashy_begin);
   uint64_t base = 0;
   uint32_t np = 0, total = 0, flags = 0;
   KeyCtx kctx;
@@ -95,21 +103,15 @@ __device__ uint32_t warp_fallback(const RouteParams& p, const uint32_t* __restri
     uint32_t wpos = 0;
     for (uint32_t s0 = 0; s0 < n_shapes; s0 += 32) {
       const uint32_t si = s0 + lane;
-      uint32_t mine = 0, g = kNone, shape_len = 0;
-      if (si < n_shapes) {
-        const uint32_t s = si < n_exact ? e0 + si : tv.hashy_begin + (si - n_exact);
-        const Shape sh = load_shape(tv, s);
-        shape_len = sh.len;
-        if (sh.len <= nw) g = probe_head(tv, s, sh, kctx);
-      }
-      // a lane can meet several groups under one shape (chained remainders): walk them in rounds
-      while (__any_sync(kFull, g != kNone)) {
+      // each lane takes one shape; a lane can meet several groups (bucket collisions, chained
+      // remainders), so the lanes walk their matches in lock-step rounds
+      uint32_t mine = 0;
+      LaneMatches lm;
+      lane_matches_begin(lm, tv, kctx, si < n_shapes, si < n_exact ? e0 + si : tv.hashy_begin + (si - n_exact));
+      for (;;) {
         GroupRec rec{};
-        bool hit = false;
-        if (g != kNone) {
-          rec = load_group(tv, g);
-          hit = rec.rem_len == 0 || remainder_matches(tv, rec, row, shape_len, nw);
-        }
+        const bool hit = lane_matches_next(lm, tv, kctx, rec);
+        if (!__any_sync(kFull, hit)) break;
         unsigned hm = __ballot_sync(kFull, hit);
         if (pass == 0) {
           if (hit) { mine += rec.list_len; flags |= rec.flags; }
@@ -122,7 +124,6 @@ __device__ uint32_t warp_fallback(const RouteParams& p, const uint32_t* __restri
             wpos += l;
           }
         }
-        g = (g != kNone) ? rec.next : kNone;
       }
       if (pass == 0) {
 #pragma unroll
@@ -157,7 +158,7 @@ __device__ uint32_t warp_fallback(const RouteParams& p, const uint32_t* __restri
 
 }  // namespace
 
-__global__ void __launch_bounds__(kRouteThreads, 4) k_route(RouteParams p) {
+__global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RouteParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   RouteSmem& sm = *reinterpret_cast<RouteSmem*>(smem_raw);
   const TableView& tv = p.tv;
@@ -180,8 +181,9 @@ __global__ void __launch_bounds__(kRouteThreads, 4) k_route(RouteParams p) {
     uint32_t k = 0, ub = 0, mxlen = 0, flags = 0, cnt = 0, nw = 0;
     const uint32_t* row = p.wid + (size_t)m * tv.wstride;
     if (m < p.n) nw = p.nwords[m];
-    if (nw > 0) {
-      auto record = [&](uint32_t, const GroupRec& rec) {
+    bool overflow = false;  // more tag hits than candidate slots: the slow path re-probes
+    if (nw > 0 && !(p.debug & 2u)) {
+      auto record = [&](const GroupRec& rec) {
         if (k < p.max_slots) { sm.loff[k][tid] = rec.list_off; sm.llen[k][tid] = rec.list_len; }
         ++k;
         ub += rec.list_len;
@@ -189,24 +191,32 @@ __global__ void __launch_bounds__(kRouteThreads, 4) k_route(RouteParams p) {
         flags |= rec.flags;
       };
       if (tv.exchange_type == 1 /* fanout */) {
-        if (tv.fanout_group != kNone) record(tv.fanout_group, load_group(tv, tv.fanout_group));
+        if (tv.fanout_group != kNone) record(load_group(tv, tv.fanout_group));
       } else {
         KeyCtx kctx;
         key_ctx_init(kctx, row, nw, tv.wstride);
-        if (nw <= (uint32_t)kLenCap) {
-          const uint32_t e1 = tv.exact_rng[2 * nw + 1];
-          for (uint32_t s = tv.exact_rng[2 * nw]; s < e1; ++s) visit_shape(tv, s, kctx, record);
-        }
-        for (uint32_t s = tv.hashy_begin; s < tv.hashy_end; ++s) {
-          if (((__ldg(reinterpret_cast<const uint32_t*>(&tv.shapes[s]) + 3) >> 8) & 0xFFu) > nw) break;
-          visit_shape(tv, s, kctx, record);
-        }
+        const uint32_t L = min(nw, (uint32_t)kLenCap);
+        const uint32_t e0 = nw <= (uint32_t)kLenCap ? tv.exact_rng[3 * L] : 0;
+        const uint32_t ne = nw <= (uint32_t)kLenCap ? tv.exact_rng[3 * L + 1] - e0 : 0;
+        const uint32_t nh = tv.exact_rng[3 * L + 2] - tv.hashy_begin;
+        uint32_t ncand = 0;
+        probe_shapes(tv, kctx, e0, ne, tv.hashy_begin, nh, [&](uint32_t slot, uint32_t shape, uint32_t lit_mask) {
+          if (ncand < (uint32_t)kRouteSlots) {
+            sm.cslot[ncand][tid] = slot;
+            sm.cshape[ncand][tid] = (shape << 16) | (lit_mask & 0xFFFFu);
+          }
+          ++ncand;
+        });
+        overflow = ncand > (uint32_t)kRouteSlots;
+        for (uint32_t c = 0; c < min(ncand, (uint32_t)kRouteSlots); ++c)
+          resolve_candidate(tv, kctx, sm.cslot[c][tid], sm.cshape[c][tid] >> 16, sm.cshape[c][tid] & 0xFFFFu, record);
       }
     }
     // classify: 0 = count known, 1 = needs the de-duplicating merge to count, 2 = slow path
     int cls = 0;
     const bool dedup = (flags & kShared) != 0;
-    if (k <= 1) cnt = ub;
+    if (overflow) cls = 2;
+    else if (k <= 1) cnt = ub;
     else if (k > p.max_slots || ub - mxlen > p.max_small) cls = 2;
     else if (dedup) cls = 1;
     else cnt = ub;
@@ -305,7 +315,7 @@ __global__ void __launch_bounds__(kRouteThreads, 4) k_route(RouteParams p) {
     __syncthreads();
 
     // ---- phase B: warps pull routed messages off the tile's queue and write their unions ----
-    const uint32_t q_n = sm.q_n;
+    const uint32_t q_n = (p.debug & 1u) ? 0u : sm.q_n;
     for (;;) {
       uint32_t qi = 0;
       if (lane == 0) qi = atomicAdd(&sm.q_next, 1u);

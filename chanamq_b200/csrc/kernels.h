@@ -7,7 +7,7 @@
 
 namespace chq {
 
-constexpr int kRouteThreads = 256;   // messages per tile; one thread per message while probing
+constexpr int kRouteThreads = 128;   // messages per tile; one thread per message while probing
 constexpr int kRouteSlots = 8;       // matched groups remembered per message before the slow path
 constexpr int kRouteSmall = 512;     // ids (all lists but the longest) a warp merges in shared memory
 
@@ -30,6 +30,7 @@ struct RouteParams {
   uint32_t* scratch;         // slow-path arena
   uint64_t scratch_cap;      // in ids
   uint32_t max_slots, max_small;
+  uint32_t debug;            // experiment switches (env CHQ_DEBUG): 1 = skip phase B, 2 = skip probing
 };
 
 cudaError_t launch_tokenize(const uint8_t* blob, const uint32_t* off, uint32_t n, const TableView& tv, int split,

@@ -127,49 +127,79 @@ __device__ uint32_t warp_union_small(const uint32_t* __restrict__ qlist, uint32_
   }
   // an id present in two short lists is emitted once
   const uint32_t prev = __shfl_up_sync(kFull, s, 1);
-  const int sdup = (dedup && lane > 0 && s == prev) ? 1 : 0;
-
-  // Stream the long list.  `dst` walks the output with the chunk; lanes past the end of the list
-  // hold kNone, so in the last chunk every remaining short id is "in range" and lands after it.
+  const bool sdup = dedup && lane > 0 && s == prev;
+  unsigned todo = __ballot_sync(kFull, (uint32_t)lane < ns && !sdup);  // short ids not yet placed, bit j = lane j
+  uint32_t s_next = todo ? __shfl_sync(kFull, s, __ffs(todo) - 1) : kNone;
+  uint32_t kept_total = 0;  // short ids placed so far
+  uint32_t my_pos = kNone;  // where this lane's short id goes, relative to pos (kNone: dropped)
   (void)cap;
-  uint32_t t = 0, kept_total = 0;
-  uint32_t s_next = __shfl_sync(kFull, s, 0);  // ns >= 1
-  const uint32_t* src = qlist + big_off + lane;
-  uint32_t* dst = WRITE ? out + pos + lane : nullptr;
-  uint32_t b_next = (uint32_t)lane < nb ? __ldg(src) : kNone;
-  for (uint32_t left = nb; left > 0; left = left > 32 ? left - 32 : 0) {
-    const uint32_t b = b_next;
-    src += 32;
-    b_next = ((uint32_t)lane + 32 < left) ? __ldg(src) : kNone;
+
+  // Weave one chunk of 32 long ids (lane value b, kNone past the end): every short id that is not
+  // above the chunk is ranked with two ballots; returns how far this lane's long id moves up.
+  auto weave = [&](uint32_t b, uint32_t base) -> uint32_t {
     const uint32_t bmax = __shfl_sync(kFull, b, 31);
-    uint32_t shift = 0;
-    if (t < ns && s_next <= bmax) {
-      const uint32_t kept0 = kept_total;
+    uint32_t shift = kept_total;
+    if (todo && s_next <= bmax) {
       do {
-        const int skip = __shfl_sync(kFull, sdup, t);
+        const int j = __ffs(todo) - 1;
         const unsigned lt = __ballot_sync(kFull, b < s_next);
         const unsigned eq = __ballot_sync(kFull, b == s_next);
-        if (!skip && eq == 0) {
+        todo &= todo - 1;
+        if (eq == 0) {
           const uint32_t p = __popc(lt);
-          if (WRITE && lane == 0) dst[p + kept_total] = s_next;
+          if (lane == j) my_pos = base + p + kept_total;
           if ((uint32_t)lane >= p) ++shift;
           ++kept_total;
         }
-        ++t;
-        s_next = t < ns ? __shfl_sync(kFull, s, t) : kNone;
-      } while (s_next <= bmax && t < ns);
-      shift += kept0;
-    } else {
-      shift = kept_total;
+        s_next = todo ? __shfl_sync(kFull, s, __ffs(todo) - 1) : kNone;
+      } while (todo && s_next <= bmax);
     }
-    if (WRITE && (uint32_t)lane < left) dst[shift] = b;
-    if (WRITE) dst += 32;
+    return shift;
+  };
+
+  // Stream the long list: full chunks without lane predicates, then the partial one.  In the partial
+  // chunk the padding lanes hold kNone, so every short id still waiting is placed there, after the list.
+  const uint32_t nfull = nb >> 5, rem = nb & 31;
+  const uint32_t* src = qlist + big_off + lane;
+  uint32_t* dst = WRITE ? out + pos + lane : nullptr;
+  uint32_t base = 0;
+  uint32_t c = 0;
+  // four chunks per round trip to L2: the loads of a round are issued together
+  for (; c + 4 <= nfull; c += 4) {
+    uint32_t b4[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) b4[u] = __ldg(src + 32 * u);
+    src += 128;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t shift = weave(b4[u], base);
+      if (WRITE) { dst[shift] = b4[u]; dst += 32; }
+      base += 32;
+    }
   }
-  // short ids that are larger than a FULL last chunk's maximum (nb a multiple of 32)
-  const bool tail = (uint32_t)lane >= t && (uint32_t)lane < ns && !sdup;
-  const unsigned tm = __ballot_sync(kFull, tail);
-  if (WRITE && tail) out[pos + nb + kept_total + __popc(tm & ((1u << lane) - 1))] = s;
-  return nb + kept_total + __popc(tm);
+  if (c < nfull) {  // one to three full chunks left
+    uint32_t b4[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) b4[u] = (c + u < nfull) ? __ldg(src + 32 * u) : 0;
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      if (c + u < nfull) {
+        const uint32_t shift = weave(b4[u], base);
+        if (WRITE) { dst[shift] = b4[u]; dst += 32; }
+        base += 32;
+        src += 32;
+      }
+    }
+  }
+  if (rem) {
+    const uint32_t b = (uint32_t)lane < rem ? __ldg(src) : kNone;
+    const uint32_t shift = weave(b, base);
+    if (WRITE && (uint32_t)lane < rem) dst[shift] = b;
+  }
+  // short ids above a list that ended on a chunk boundary
+  if ((todo >> lane) & 1u) my_pos = nb + kept_total + __popc(todo & ((1u << lane) - 1));
+  if (WRITE && my_pos != kNone) out[pos + my_pos] = s;
+  return nb + kept_total + __popc(todo);
 }
 
 // Lane j < k holds list j = qlist[my_off .. my_off + my_len).  Precondition: the lists other than

@@ -1,5 +1,10 @@
 // Device-side probing of the compiled table (included by kernels.cu only): word dictionary,
 // tuple-space hash probe with exact verification, and the word-level NFA for '#' remainders.
+//
+// Probing is latency work (random 16-byte reads of an L2-resident tag array), so it is organised
+// for memory-level parallelism: a key hashes FOUR shapes at a time and issues their tag loads
+// together; tag hits are only noted (slot, shape) and resolved afterwards — group record and
+// literal tuple arrive in one 64-byte read — so no dependent load sits inside the probe loop.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -12,7 +17,6 @@ namespace {
 constexpr unsigned kFull = 0xFFFFFFFFu;
 
 __device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
-
 
 // ------------------------------------------------------------------------------------------
 // word dictionary probe (exact: hash, length, first 8 bytes, then the remaining bytes)
@@ -39,19 +43,18 @@ __device__ uint32_t dict_lookup(const TableView& tv, uint64_t fnv, uint64_t f8, 
   }
 }
 
-
 // ------------------------------------------------------------------------------------------
-// probing
+// table records
 // ------------------------------------------------------------------------------------------
 struct GroupRec {
-  uint32_t list_off, list_len, lit_off, next, rem_off, rem_len, nlit, flags;
+  uint32_t list_off, list_len, next, shape, flags;
 };
+// The head 16 bytes of a group record (one lane-load).
 __device__ __forceinline__ GroupRec load_group(const TableView& tv, uint32_t g) {
   const uint4 a = ldg16(&tv.groups[g]);
-  const uint4 b = ldg16(reinterpret_cast<const uint8_t*>(&tv.groups[g]) + 16);
   GroupRec r;
-  r.list_off = a.x; r.list_len = a.y; r.lit_off = a.z; r.next = a.w;
-  r.rem_off = b.x; r.rem_len = b.y & 0xFFFFu; r.nlit = (b.y >> 16) & 0xFFu; r.flags = b.y >> 24;
+  r.list_off = a.x; r.list_len = a.y; r.next = a.z;
+  r.shape = a.w & 0xFFFFu; r.flags = a.w >> 24;
   return r;
 }
 
@@ -72,7 +75,7 @@ struct KeyCtx {
   uint32_t z[8];
   const uint32_t* row;
   uint32_t nw;
-  uint32_t unknown;   // bit p: word p is kUnknownWord (can only meet a wildcard)
+  uint32_t unknown;   // bit p: word p is kUnknownWord or past the key's end (can only meet a wildcard)
 };
 __device__ __forceinline__ void key_ctx_init(KeyCtx& k, const uint32_t* __restrict__ row, uint32_t nw, uint32_t wstride) {
   k.row = row;
@@ -94,10 +97,10 @@ __device__ __forceinline__ void key_ctx_init(KeyCtx& k, const uint32_t* __restri
   }
 }
 
-// Head group of the chain whose (shape, literal tuple) equals the key's words at the shape's
-// literal positions, or kNone.  Exact: on a tag hit the stored tuple is compared word by word.
-__device__ __forceinline__ uint32_t probe_head(const TableView& tv, uint32_t shape_idx, const Shape& sh, const KeyCtx& k) {
-  if (sh.lit_mask & k.unknown & 0xFFu) return kNone;
+// Hash of the key's words at the shape's literal positions; false when one of them is a word no
+// binding mentions (then nothing under this shape can match).
+__device__ __forceinline__ bool shape_hash(const Shape& sh, const KeyCtx& k, uint32_t& h_out) {
+  if (sh.lit_mask & k.unknown & 0xFFu) return false;
   uint32_t h = (uint32_t)sh.seed;
 #pragma unroll
   for (int p = 0; p < 8; ++p)
@@ -105,43 +108,67 @@ __device__ __forceinline__ uint32_t probe_head(const TableView& tv, uint32_t sha
   for (uint32_t m = sh.lit_mask >> 8; m; m &= m - 1) {  // literal positions 8..15: rare, on the fly
     const uint32_t p = 8 + (__ffs(m) - 1);
     const uint32_t w = __ldg(k.row + p);
-    if (w == kUnknownWord) return kNone;
+    if (w == kUnknownWord) return false;
     h ^= zob(p, w);
   }
-  const uint32_t tag = tag32(h);
-  uint32_t b = h & tv.bucket_mask;
-  for (;;) {
-    const uint4 s01 = ldg16(&tv.slots[(size_t)b * 4]);
-    const uint4 s23 = ldg16(&tv.slots[(size_t)b * 4 + 2]);
-    const bool any_hit = (s01.x == tag) | (s01.z == tag) | (s23.x == tag) | (s23.z == tag);
-    if (any_hit) {
-      const uint32_t tags[4] = {s01.x, s01.z, s23.x, s23.z};
-      const uint32_t grps[4] = {s01.y, s01.w, s23.y, s23.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        if (tags[i] != tag) continue;
-        const uint32_t g = grps[i];
-        const Group* gp = &tv.groups[g];
-        if (__ldg(&gp->shape) != shape_idx) continue;
-        const uint32_t lit_off = __ldg(&gp->lit_off);
-        bool same = true;
-        uint32_t li = 0;
-        for (uint32_t m = sh.lit_mask; m; m &= m - 1, ++li)
-          if (__ldg(tv.lits + lit_off + li) != __ldg(k.row + (__ffs(m) - 1))) { same = false; break; }
-        if (same) return g;
-      }
-    }
-    if ((s01.x == 0) | (s01.z == 0) | (s23.x == 0) | (s23.z == 0)) return kNone;  // bucket not full: chain ends
-    b = (b + 1) & tv.bucket_mask;
+  h_out = h;
+  return true;
+}
+
+// eight 16-bit tags against one: bit i of the result = slot i matches; full = no empty slot
+__device__ __forceinline__ uint32_t match_tags(const uint4& t, uint32_t tag, bool& full) {
+  const uint32_t tt = tag * 0x10001u;
+  const uint32_t c0 = __vcmpeq2(t.x, tt), c1 = __vcmpeq2(t.y, tt), c2 = __vcmpeq2(t.z, tt), c3 = __vcmpeq2(t.w, tt);
+  full = (__vcmpeq2(t.x, 0) | __vcmpeq2(t.y, 0) | __vcmpeq2(t.z, 0) | __vcmpeq2(t.w, 0)) == 0;
+  if ((c0 | c1 | c2 | c3) == 0) return 0;
+  return (c0 & 1u) | ((c0 >> 15) & 2u) | ((c1 & 1u) << 2) | ((c1 >> 13) & 8u) | ((c2 & 1u) << 4) | ((c2 >> 11) & 32u) |
+         ((c3 & 1u) << 6) | ((c3 >> 9) & 128u);
+}
+
+__device__ bool remainder_matches(const TableView& tv, uint32_t rem_off, uint32_t rem_len, const uint32_t* __restrict__ row,
+                                  uint32_t from, uint32_t nw);
+
+// Exact check of a candidate: the group must belong to the probing shape and its literal tuple
+// must equal the key's words at the shape's literal positions.  Positions 0..7 are compared as
+// zob values held in registers (zob(p, .) is a bijection, so this is word equality); the second
+// half of zpos[] is only fetched when the shape has a literal there.
+__device__ __forceinline__ bool verify_group(const TableView& tv, uint32_t g, const GroupRec& rec, uint32_t shape_idx,
+                                             uint32_t lit_mask, const KeyCtx& k) {
+  if (rec.shape != shape_idx) return false;
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(&tv.groups[g]);
+  const uint4 lo = ldg16(base + 16);
+  bool ok = true;
+  if (lit_mask & 1u) ok = ok && lo.x == k.z[0];
+  if (lit_mask & 2u) ok = ok && lo.y == k.z[1];
+  if (lit_mask & 4u) ok = ok && lo.z == k.z[2];
+  if (lit_mask & 8u) ok = ok && lo.w == k.z[3];
+  if (lit_mask & 0xF0u) {
+    const uint4 hi = ldg16(base + 32);
+    if (lit_mask & 16u) ok = ok && hi.x == k.z[4];
+    if (lit_mask & 32u) ok = ok && hi.y == k.z[5];
+    if (lit_mask & 64u) ok = ok && hi.z == k.z[6];
+    if (lit_mask & 128u) ok = ok && hi.w == k.z[7];
   }
+  if (ok && (lit_mask >> 8)) {  // literals at positions 8..15: compare the word ids themselves
+    const uint32_t lit_off = __ldg(&tv.groups[g].lit_off);
+    uint32_t i = __popc(lit_mask & 0xFFu);
+    for (uint32_t m = lit_mask >> 8; m && ok; m &= m - 1, ++i)
+      ok = __ldg(tv.lits + lit_off + i) == __ldg(k.row + 8 + (__ffs(m) - 1));
+  }
+  return ok;
+}
+// the remainder of group g (if any) against the key's words from position `from`
+__device__ __forceinline__ bool group_rem_ok(const TableView& tv, uint32_t g, const GroupRec& rec, const KeyCtx& k, uint32_t from) {
+  if (!(rec.flags & kHasRem)) return true;
+  return remainder_matches(tv, __ldg(&tv.groups[g].rem_off), __ldg(&tv.groups[g].rem_len), k.row, from, k.nw);
 }
 
 // Word-level NFA for a pattern remainder (literals, '*', '#') against key words [from, nw).
 // State s = remainder items consumed so far; '#' may take zero or more words.
-__device__ bool remainder_matches(const TableView& tv, const GroupRec& g, const uint32_t* __restrict__ row,
+__device__ bool remainder_matches(const TableView& tv, uint32_t rem_off, uint32_t rem_len, const uint32_t* __restrict__ row,
                                   uint32_t from, uint32_t nw) {
-  const uint32_t r = g.rem_len;
-  const uint32_t* rem = tv.rems + g.rem_off;
+  const uint32_t r = rem_len;
+  const uint32_t* rem = tv.rems + rem_off;
   // reach bitset over states 0..r (r <= 128): 5 words
   uint32_t cur[5] = {1u, 0, 0, 0, 0}, nxt[5];
   auto close = [&](uint32_t* st) {  // epsilon: a '#' can be skipped
@@ -167,16 +194,119 @@ __device__ bool remainder_matches(const TableView& tv, const GroupRec& g, const 
   return (cur[r >> 5] >> (r & 31)) & 1u;
 }
 
-// Calls f(group index, record) for every group that matches this key.
+// Pass 1 of a key's lookup: probe every shape in [e0, e0+ne) and [h0, h0+nh), four at a time.
+// on_cand(slot index, shape index, literal mask) is called for every tag hit; nothing is dereferenced here.
 template <typename F>
-__device__ __forceinline__ void visit_shape(const TableView& tv, uint32_t s, const KeyCtx& k, F&& f) {
-  const Shape sh = load_shape(tv, s);
-  uint32_t g = probe_head(tv, s, sh, k);
-  while (g != kNone) {
-    const GroupRec rec = load_group(tv, g);
-    if (rec.rem_len == 0 || remainder_matches(tv, rec, k.row, sh.len, k.nw)) f(g, rec);
-    g = rec.next;
+__device__ __forceinline__ void probe_shapes(const TableView& tv, const KeyCtx& k, uint32_t e0, uint32_t ne, uint32_t h0,
+                                             uint32_t nh, F&& on_cand) {
+#ifndef CHQ_PROBE_BATCH
+#define CHQ_PROBE_BATCH 1
+#endif
+  constexpr int kB = CHQ_PROBE_BATCH;
+  const uint32_t total = ne + nh;
+  for (uint32_t i = 0; i < total; i += kB) {
+    uint32_t sidx[kB], hh[kB], lmask[kB];
+    uint4 tg[kB];
+    bool live[kB];
+#pragma unroll
+    for (int u = 0; u < kB; ++u) {
+      const uint32_t ii = i + u;
+      live[u] = ii < total;
+      sidx[u] = ii < ne ? e0 + ii : h0 + (ii - ne);
+      hh[u] = 0;
+      lmask[u] = 0;
+      if (live[u]) {
+        const Shape sh = load_shape(tv, sidx[u]);
+        lmask[u] = sh.lit_mask;
+        live[u] = shape_hash(sh, k, hh[u]);
+      }
+      if (live[u]) tg[u] = ldg16(tv.tags + (size_t)(hh[u] & tv.bucket_mask) * kBucketSlots);
+    }
+#pragma unroll
+    for (int u = 0; u < kB; ++u) {
+      if (!live[u]) continue;
+      const uint32_t tag = tag16(hh[u]);
+      uint32_t b = hh[u] & tv.bucket_mask;
+      uint4 t = tg[u];
+      for (;;) {
+        bool full;
+        uint32_t m = match_tags(t, tag, full);
+        for (; m; m &= m - 1) on_cand(b * kBucketSlots + (__ffs(m) - 1), sidx[u], lmask[u]);
+        if (!full) break;
+        b = (b + 1) & tv.bucket_mask;  // the bucket overflowed at build time: keep going (rare)
+        t = ldg16(tv.tags + (size_t)b * kBucketSlots);
+      }
+    }
   }
+}
+
+// Pass 2: resolve one candidate.  f(record) is called for every group that really matches.
+template <typename F>
+__device__ __forceinline__ void resolve_candidate(const TableView& tv, const KeyCtx& k, uint32_t slot, uint32_t shape_idx,
+                                                  uint32_t lit_mask, F&& f) {
+  uint32_t g = __ldg(tv.slot_group + slot);
+  GroupRec rec = load_group(tv, g);
+  if (!verify_group(tv, g, rec, shape_idx, lit_mask, k)) return;
+  for (;;) {  // a chain shares one literal tuple and differs in its remainders
+    if (!(rec.flags & kHasRem)) f(rec);
+    else if (group_rem_ok(tv, g, rec, k, (uint32_t)__ldg(&tv.shapes[shape_idx].len))) f(rec);
+    g = rec.next;
+    if (g == kNone) return;
+    rec = load_group(tv, g);
+  }
+}
+
+// Slow-path iterator: all groups matching this key under ONE shape, one per call (the warp-level
+// slow path gives every lane its own shape and steps the lanes together).
+struct LaneMatches {
+  uint4 t;
+  uint32_t shape, lit_mask, len, tag, b, m, g;
+  bool live, full;
+};
+__device__ __forceinline__ void lane_matches_begin(LaneMatches& lm, const TableView& tv, const KeyCtx& k, bool active,
+                                                   uint32_t shape_idx) {
+  lm.live = active;
+  lm.g = kNone;
+  lm.m = 0;
+  lm.full = false;
+  if (!active) return;
+  const Shape sh = load_shape(tv, shape_idx);
+  uint32_t h = 0;
+  lm.live = sh.len <= k.nw && shape_hash(sh, k, h);
+  if (!lm.live) return;
+  lm.shape = shape_idx;
+  lm.lit_mask = sh.lit_mask;
+  lm.len = sh.len;
+  lm.tag = tag16(h);
+  lm.b = h & tv.bucket_mask;
+  lm.t = ldg16(tv.tags + (size_t)lm.b * kBucketSlots);
+  lm.m = match_tags(lm.t, lm.tag, lm.full);
+}
+__device__ __forceinline__ bool lane_matches_next(LaneMatches& lm, const TableView& tv, const KeyCtx& k, GroupRec& rec) {
+  while (lm.live) {
+    if (lm.g != kNone) {  // further groups with the same literal tuple (other remainders)
+      const uint32_t g = lm.g;
+      rec = load_group(tv, g);
+      lm.g = rec.next;
+      if (group_rem_ok(tv, g, rec, k, lm.len)) return true;
+    } else if (lm.m) {
+      const uint32_t slot = lm.b * kBucketSlots + (__ffs(lm.m) - 1);
+      lm.m &= lm.m - 1;
+      const uint32_t g = __ldg(tv.slot_group + slot);
+      rec = load_group(tv, g);
+      if (verify_group(tv, g, rec, lm.shape, lm.lit_mask, k)) {
+        lm.g = rec.next;
+        if (group_rem_ok(tv, g, rec, k, lm.len)) return true;
+      }
+    } else if (lm.full) {
+      lm.b = (lm.b + 1) & tv.bucket_mask;
+      lm.t = ldg16(tv.tags + (size_t)lm.b * kBucketSlots);
+      lm.m = match_tags(lm.t, lm.tag, lm.full);
+    } else {
+      lm.live = false;
+    }
+  }
+  return false;
 }
 
 }  // namespace
