@@ -59,6 +59,7 @@ def load_library():
         "chq_route_submit": (i32, [vp, i32, vp, vp, u32]),
         "chq_route_wait": (i32, [vp, i32, C.POINTER(ChqResult)]),
         "chq_route_device": (i32, [vp, vp, vp, u32, vp, vp, u64, vp, vp, vp, vp, vp]),
+        "chq_route_device_static": (i32, [vp, vp, vp, u32, vp, vp, u64, vp, vp, vp, vp, vp]),
         "chq_host_alloc": (i32, [C.POINTER(vp), u64]),
         "chq_host_free": (i32, [vp]),
         "chq_stats": (i32, [vp, C.c_char_p, u32]),

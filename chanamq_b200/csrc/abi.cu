@@ -490,6 +490,102 @@ int32_t chq_route_device(chq_table* t, const uint8_t* d_keys_blob, const uint32_
                        d_err, d_total, d_status, (cudaStream_t)stream);
 }
 
+// ---------------------------------------------------------------------------------------------
+// chq_route_device_static: the same tokenise + route launches as chq_route_device, for callers
+// that must not allocate.  Everything the launches need beyond the caller's inputs and outputs
+// (scan state, the interned-word rows, the slow-path merge arena) lives in ONE fixed array that is
+// part of the library image on every GPU that loads it.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr uint32_t kStaticMaxKeys = CHQ_STATIC_MAX_KEYS;     // keys per call
+constexpr uint32_t kStaticMaxWords = CHQ_STATIC_MAX_WORDS;   // keys x word-id stride of the table
+constexpr uint32_t kStaticArenaIds = 1u << 20;               // slow-path merge arena, in queue ids
+constexpr size_t kStaticTiles = (kStaticMaxKeys + kRouteThreads - 1) / kRouteThreads;
+constexpr size_t kStaticOffState = 0;                                                   // u64[2 + tiles]
+constexpr size_t kStaticOffNwords = ((2 + kStaticTiles) * 8 + 255) & ~size_t(255);      // u8[keys]
+constexpr size_t kStaticOffWid = (kStaticOffNwords + kStaticMaxKeys + 255) & ~size_t(255);  // u32[words]
+constexpr size_t kStaticOffArena = kStaticOffWid + (size_t)kStaticMaxWords * 4;         // u32[arena]
+constexpr size_t kStaticBytes = kStaticOffArena + (size_t)kStaticArenaIds * 4;
+
+// About 6.3 MiB of device memory, held by every GPU that loads this library until the process exits.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+// In host code the name g_static_scratch is only a handle for the runtime, not a device address;
+// the address a kernel can use comes from cudaGetSymbolAddress, asked once per device.
+unsigned char* g_static_ptr[64] = {};
+
+int static_scratch_ptr(int device, unsigned char** out) {
+  if (device < 0 || device >= 64) return fail(CHQ_E_ARG, "chq_route_device_static: device ordinal out of range");
+  if (!g_static_ptr[device]) {
+    void* p = nullptr;
+    CU(cudaGetSymbolAddress(&p, g_static_scratch));  // the table's device is current here
+    g_static_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_ptr[device];
+  return CHQ_OK;
+}
+
+}  // namespace
+
+int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const uint32_t* d_key_offsets, uint32_t n,
+                                uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,
+                                uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream) {
+  if (!t || !d_offsets || !d_total || !d_status || (n && (!d_key_offsets || !d_any_durable || !d_err)))
+    return fail(CHQ_E_ARG, "chq_route_device_static: bad argument");
+  if (t->host_only) return fail(CHQ_E_CUDA, "chq_route_device_static: host-only table (device -1) cannot route");
+  if (!t->committed) return fail(CHQ_E_NOT_COMMITTED, "chq_route_device_static: table has uncommitted binds");
+  if (n > kStaticMaxKeys)
+    return fail(CHQ_E_ARG, "chq_route_device_static: more than CHQ_STATIC_MAX_KEYS keys in one call (split the batch, or "
+                           "use chq_route_device, which allocates)");
+  if ((uint64_t)n * t->tv.wstride > kStaticMaxWords)
+    return fail(CHQ_E_ARG, "chq_route_device_static: keys x the table's word stride exceeds CHQ_STATIC_MAX_WORDS (tables "
+                           "with '#' inside a pattern keep 128 words per key: send fewer keys per call)");
+  int rc = set_device(t);
+  if (rc) return rc;
+  unsigned char* base = nullptr;
+  if ((rc = static_scratch_ptr(t->device, &base))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const uint32_t n_tiles = (n + kRouteThreads - 1) / kRouteThreads;
+  uint64_t* state = reinterpret_cast<uint64_t*>(base + kStaticOffState);
+  // the array keeps whatever the previous call left: the control words and the per-tile scan state
+  // must start at zero; the rows, counts and arena are fully rewritten before they are read
+  CU(cudaMemsetAsync(state, 0, ((size_t)n_tiles + 2) * sizeof(uint64_t), st));
+  if (n == 0) {
+    CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
+    CU(cudaMemsetAsync(d_total, 0, sizeof(uint64_t), st));
+    CU(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+    return CHQ_OK;
+  }
+  uint8_t* nwords = base + kStaticOffNwords;
+  uint32_t* wid = reinterpret_cast<uint32_t*>(base + kStaticOffWid);
+  const int split = (t->host.type() == CHQ_TOPIC || t->host.type() == CHQ_HEADERS) ? 1 : 0;
+  CU(launch_tokenize(d_keys_blob, d_key_offsets, n, t->tv, split, wid, nwords, d_err, st));
+  RouteParams p{};
+  p.tv = t->tv;
+  p.wid = wid;
+  p.nwords = nwords;
+  p.n = n;
+  p.n_tiles = n_tiles;
+  p.offsets = d_offsets;
+  p.ids = d_queue_ids;
+  p.ids_cap = ids_cap;
+  p.durable = d_any_durable;
+  p.total = d_total;
+  p.ctrl = reinterpret_cast<uint32_t*>(state);
+  p.tile_state = state + 2;
+  p.scratch = reinterpret_cast<uint32_t*>(base + kStaticOffArena);
+  p.scratch_cap = kStaticArenaIds;
+  p.max_slots = t->max_slots;
+  p.max_small = t->max_small;
+  p.debug = 0;
+  CU(launch_route(p, t->n_sms, st));
+  CU(launch_finish(p.ctrl, d_status, st));
+  t->n_batches++;
+  t->n_messages += n;
+  return CHQ_OK;
+}
+
 int32_t chq_host_alloc(void** p, uint64_t bytes) {
   if (!p) return fail(CHQ_E_ARG, "chq_host_alloc: bad argument");
   CU(cudaMallocHost(p, bytes ? bytes : 1));

@@ -188,6 +188,14 @@ class GpuMatcher:
         check(self.L.chq_route_wait(self.h, slot, C.byref(res)))
         return self._result(res, copy)
 
+    def route_device_static(self, d_blob, d_off, n, d_offsets, d_ids, ids_cap, d_durable, d_err, d_total, d_status,
+                            stream=0):
+        """chq_route_device_static: same arguments and results as route_device, but the call allocates
+        nothing (fixed in-library scratch; at most CHQ_STATIC_MAX_KEYS keys; calls must not overlap)"""
+        self._ensure()
+        check(self.L.chq_route_device_static(self.h, d_blob, d_off, n, d_offsets, d_ids, ids_cap, d_durable, d_err,
+                                             d_total, d_status, stream))
+
     def lookup_all(self, keys):
         """list of keys -> per key the sorted list of queue names (bytes), None where the reference throws"""
         blob, off = pack(keys)

@@ -107,6 +107,38 @@ int32_t chq_route_device(chq_table* t, const uint8_t* d_keys_blob, const uint32_
                          uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,
                          uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream);
 
+/* No counterpart in the reference (it has no device code at all); added for embedders that are not
+ * allowed to allocate.
+ *
+ * Same contract and same kernels as chq_route_device, but the call allocates NOTHING: no cudaMalloc,
+ * no cudaFree, no allocating library routine.  Who needs that: a broker thread that routes inside a
+ * latency budget and cannot afford a cudaMalloc (it synchronises the whole device and can stall for
+ * milliseconds while other streams are busy); a process that has handed all device memory to a pool
+ * and would get cudaErrorMemoryAllocation from a fresh request; a deployment whose rule is that
+ * nothing is allocated after start-up, so that steady-state routing can never fail for lack of memory.
+ *
+ * The scratch the two launches need (prefix-sum state, the interned word ids of the batch, the arena
+ * of the rare merge slow path) sits in one fixed array inside the library image: about 6.3 MiB of
+ * device memory on every GPU that loads libchanagpu.so, held until the process exits.  Hence the limits:
+ *   n                        <= CHQ_STATIC_MAX_KEYS  (65 536 keys per call)
+ *   n x the table's word stride <= CHQ_STATIC_MAX_WORDS (524 288; the stride is 8 for ordinary tables,
+ *                               so the first limit is the one that bites; it is 128 when a pattern has
+ *                               '#' before its end, which leaves 4 096 keys per call)
+ * A larger request is refused with CHQ_E_ARG and a message saying which limit was hit; nothing is
+ * launched.  The slow-path arena holds 1 Mi queue ids; a batch that needs more reports CHQ_E_SCRATCH
+ * in *d_status, exactly like chq_route_device.
+ *
+ * The first call on a device looks up the array's device address (cudaGetSymbolAddress) and sizes
+ * the launch; make that first call during start-up, before any stream capture begins.
+ * All calls share the one array, and it keeps the previous call's contents (the function clears the
+ * part that has to start at zero).  Two calls whose work overlaps on the GPU — different streams,
+ * different tables, different threads — race on it and corrupt each other: serialise them. */
+#define CHQ_STATIC_MAX_KEYS 65536u
+#define CHQ_STATIC_MAX_WORDS 524288u
+int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const uint32_t* d_key_offsets, uint32_t n,
+                                uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,
+                                uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream);
+
 /* pinned host memory for callers that want zero-copy staging (JNA: new Pointer(addr)) */
 int32_t chq_host_alloc(void** p, uint64_t bytes);
 int32_t chq_host_free(void* p);
