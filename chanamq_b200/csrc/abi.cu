@@ -193,7 +193,7 @@ int upload_table(chq_table* t) {
 }
 
 // Enqueue tokenise + route for n keys already on the device.  Everything is asynchronous on st.
-int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint32_t* d_off, uint32_t n,
+int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint32_t* d_off, const uint32_t* d_klen, uint32_t n,
                   uint32_t* d_offsets, uint32_t* d_ids, uint64_t ids_cap, uint8_t* d_durable, uint8_t* d_err,
                   uint64_t* d_total, int32_t* d_status, cudaStream_t st) {
   const uint32_t n_tiles = (n + kRouteThreads - 1) / kRouteThreads;
@@ -217,7 +217,8 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
       if (!pe[i]) CU(cudaEventCreate(&pe[i]));
     CU(cudaEventRecord(pe[0], st));
   }
-  CU(launch_tokenize(d_blob, d_off, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
+  if (d_klen) CU(launch_tokenize_keys(d_blob, d_off, d_klen, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
+  else CU(launch_tokenize(d_blob, d_off, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
   if (pe) CU(cudaEventRecord(pe[1], st));
   RouteParams p{};
   p.tv = t->tv;
@@ -261,7 +262,7 @@ int slot_init(RouteSlot& s) {
 }
 
 int slot_launch(chq_table* t, RouteSlot& s) {
-  int rc = enqueue_route(t, s.ws, s.d_blob.p, s.d_off.p, s.n, s.d_offsets.p, s.d_ids.p, s.d_ids.cap, s.d_durable.p,
+  int rc = enqueue_route(t, s.ws, s.d_blob.p, s.d_off.p, nullptr, s.n, s.d_offsets.p, s.d_ids.p, s.d_ids.cap, s.d_durable.p,
                          s.d_err.p, s.d_total.p, reinterpret_cast<int32_t*>(s.d_total.p + 1), s.st);
   if (rc) return rc;
   CU(cudaMemcpyAsync(s.r_total.p, s.d_total.p, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.st));
@@ -486,7 +487,20 @@ int32_t chq_route_device(chq_table* t, const uint8_t* d_keys_blob, const uint32_
   if (!t->committed) return fail(CHQ_E_NOT_COMMITTED, "chq_route_device: table has uncommitted binds");
   int rc = set_device(t);
   if (rc) return rc;
-  return enqueue_route(t, t->dev_ws, d_keys_blob, d_key_offsets, n, d_offsets, d_queue_ids, ids_cap, d_any_durable,
+  return enqueue_route(t, t->dev_ws, d_keys_blob, d_key_offsets, nullptr, n, d_offsets, d_queue_ids, ids_cap, d_any_durable,
+                       d_err, d_total, d_status, (cudaStream_t)stream);
+}
+
+int32_t chq_route_keys_device(chq_table* t, const uint8_t* d_bytes, const uint32_t* d_key_off, const uint32_t* d_key_len,
+                              uint32_t n, uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap,
+                              uint8_t* d_any_durable, uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream) {
+  if (!t || !d_offsets || !d_total || !d_status || (n && (!d_key_off || !d_key_len || !d_any_durable || !d_err)))
+    return fail(CHQ_E_ARG, "chq_route_keys_device: bad argument");
+  if (t->host_only) return fail(CHQ_E_CUDA, "chq_route_keys_device: host-only table (device -1) cannot route");
+  if (!t->committed) return fail(CHQ_E_NOT_COMMITTED, "chq_route_keys_device: table has uncommitted binds");
+  int rc = set_device(t);
+  if (rc) return rc;
+  return enqueue_route(t, t->dev_ws, d_bytes, d_key_off, d_key_len, n, d_offsets, d_queue_ids, ids_cap, d_any_durable,
                        d_err, d_total, d_status, (cudaStream_t)stream);
 }
 

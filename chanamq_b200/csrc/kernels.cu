@@ -30,12 +30,15 @@ namespace chq {
 
 // One thread per key.  Java split semantics: words are cut at every '.', trailing
 // empty words are dropped, a key without any '.' is one word (even when empty).
+// Key i is blob[off[i] .. off[i+1]) (klen == null: keys packed back to back) or blob[off[i] .. off[i]+klen[i])
+// (keys scattered inside a byte batch, as the frame decoder leaves them).
 __global__ void __launch_bounds__(256) k_tokenize(const uint8_t* __restrict__ blob, const uint32_t* __restrict__ off,
-                                                  uint32_t n, TableView tv, int split, uint32_t* __restrict__ wid,
-                                                  uint8_t* __restrict__ nwords, uint8_t* __restrict__ err) {
+                                                  const uint32_t* __restrict__ klen, uint32_t n, TableView tv, int split,
+                                                  uint32_t* __restrict__ wid, uint8_t* __restrict__ nwords,
+                                                  uint8_t* __restrict__ err) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const uint32_t b0 = off[i], b1 = off[i + 1];
+  const uint32_t b0 = off[i], b1 = klen ? b0 + klen[i] : off[i + 1];
   if (b1 - b0 > (uint32_t)kMaxKeyBytes) { nwords[i] = 0; err[i] = 2; return; }
   uint32_t* row = wid + (size_t)i * tv.wstride;
   uint32_t cnt = 0, last_nonempty = 0, wl = 0, wstart = b0;
@@ -353,11 +356,20 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
 // ------------------------------------------------------------------------------------------
 static unsigned long long g_launches = 0;
 unsigned long long kernel_launches() { return g_launches; }
+void note_launches(int n) { g_launches += (unsigned long long)n; }
 
 cudaError_t launch_tokenize(const uint8_t* blob, const uint32_t* off, uint32_t n, const TableView& tv, int split,
                             uint32_t* wid, uint8_t* nwords, uint8_t* err, cudaStream_t st) {
   if (n == 0) return cudaSuccess;
-  k_tokenize<<<(n + 255) / 256, 256, 0, st>>>(blob, off, n, tv, split, wid, nwords, err);
+  k_tokenize<<<(n + 255) / 256, 256, 0, st>>>(blob, off, nullptr, n, tv, split, wid, nwords, err);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tokenize_keys(const uint8_t* bytes, const uint32_t* key_off, const uint32_t* key_len, uint32_t n,
+                                 const TableView& tv, int split, uint32_t* wid, uint8_t* nwords, uint8_t* err, cudaStream_t st) {
+  if (n == 0) return cudaSuccess;
+  k_tokenize<<<(n + 255) / 256, 256, 0, st>>>(bytes, key_off, key_len, n, tv, split, wid, nwords, err);
   ++g_launches;
   return cudaGetLastError();
 }

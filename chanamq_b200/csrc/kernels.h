@@ -35,6 +35,9 @@ struct RouteParams {
 
 cudaError_t launch_tokenize(const uint8_t* blob, const uint32_t* off, uint32_t n, const TableView& tv, int split,
                             uint32_t* wid, uint8_t* nwords, uint8_t* err, cudaStream_t st);
+cudaError_t launch_tokenize_keys(const uint8_t* bytes, const uint32_t* key_off, const uint32_t* key_len, uint32_t n,
+                                 const TableView& tv, int split, uint32_t* wid, uint8_t* nwords, uint8_t* err, cudaStream_t st);
+void note_launches(int n);
 cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st);
 cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t st);
 unsigned long long kernel_launches();

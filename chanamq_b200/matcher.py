@@ -188,6 +188,13 @@ class GpuMatcher:
         check(self.L.chq_route_wait(self.h, slot, C.byref(res)))
         return self._result(res, copy)
 
+    def route_keys_device(self, d_bytes, d_key_off, d_key_len, n, d_offsets, d_ids, ids_cap, d_durable, d_err, d_total,
+                          d_status, stream=0):
+        """chq_route_keys_device: keys scattered inside a device byte batch (as the frame decoder leaves them)"""
+        self._ensure()
+        check(self.L.chq_route_keys_device(self.h, d_bytes, d_key_off, d_key_len, n, d_offsets, d_ids, ids_cap, d_durable,
+                                           d_err, d_total, d_status, stream))
+
     def route_device_static(self, d_blob, d_off, n, d_offsets, d_ids, ids_cap, d_durable, d_err, d_total, d_status,
                             stream=0):
         """chq_route_device_static: same arguments and results as route_device, but the call allocates

@@ -61,6 +61,23 @@ class TopicWorkload:
         return blob[:max(int(used), 1)], off, q, d
 
 
+def amqp_stream(topic, target_bytes, n_seg, body_bytes=4096, stream=0, out=None):
+    """AMQP 0-9-1 publish stream of SURVEY.md §8(d) config 5 -> (bytes uint8[], seg_offsets uint64[n_seg+1], n_messages).
+    `topic` is a TopicWorkload (routing keys come from it); `out` may be a preallocated (pinned) buffer."""
+    L = _lib()
+    L.chqgen_amqp_max_message.restype = C.c_uint64
+    L.chqgen_amqp_max_message.argtypes = [C.c_uint32]
+    L.chqgen_amqp_stream.restype = C.c_uint64
+    L.chqgen_amqp_stream.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint64,
+                                     C.c_void_p, C.POINTER(C.c_uint64)]
+    buf = out if out is not None else np.empty(int(target_bytes) + 64, dtype=np.uint8)
+    seg = np.zeros(n_seg + 1, dtype=np.uint64)
+    n_msgs = C.c_uint64(0)
+    used = L.chqgen_amqp_stream(topic.g, stream, int(target_bytes), n_seg, body_bytes, buf.ctypes.data, int(buf.size),
+                                seg.ctypes.data, C.byref(n_msgs))
+    return buf[: int(used)], seg, int(n_msgs.value)
+
+
 def queue_names_packed(queue_idx):
     """queue index -> name "q%07u", packed (blob, off); ascending index = ascending name"""
     n = len(queue_idx)

@@ -139,6 +139,57 @@ int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const 
                                 uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,
                                 uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream);
 
+/* ---- decode seam: FrameParser.onReceive (chana-mq-base/.../engine/FrameParser.scala:78-158) +
+ *      CommandAssembler.onReceive (.../engine/CommandAssembler.scala:56-130) + Basic.Publish arguments
+ *      (.../method/Basic.scala:45) + BasicProperties.readFrom (.../model/BasicProperties.scala:42-96) + the
+ *      publish fields FrameStage derives (engine/FrameStage.scala:483-508), for MANY connection segments at once.
+ *
+ *      bytes[seg_offsets[s] .. seg_offsets[s+1]) is what connection s has received and not yet consumed; it
+ *      must start on a frame boundary.  The call is stateless: seg_consumed[s] = bytes up to the end of the
+ *      last COMPLETE command (or idle heartbeat); the caller keeps the rest and prepends it next time (the
+ *      reference keeps that tail inside FrameParser / CommandAssembler instead).  One record per assembled
+ *      command, segment by segment in stream order.  seg_err[s]: 0, 501 = FRAME_ERROR (bad end marker,
+ *      wrong frame type for the assembler state, body overshoot; chana-mq-base/.../model/ErrorCodes.scala:17)
+ *      or 1 = the reference throws here (unknown class id, truncated payload, continuation flag, negative
+ *      size); the segment stops at its first error, seg_err_off[s] = the offending frame, and the records
+ *      before it are still returned (FrameStage discards them and closes: engine/FrameStage.scala:320-335).
+ *      Heartbeat frames are skipped (engine/FrameStage.scala:301-303). ---- */
+typedef struct {
+  uint64_t method_off;  /* offset of the METHOD frame in `bytes` */
+  uint64_t body_off;    /* payload of the first non-empty BODY frame (0: none) */
+  uint64_t body_size;   /* bodySize of the content header (what the BODY frames carry in total) */
+  int64_t ttl;          /* expiration as Long.parseLong reads it; valid if CHQ_PUB_HAS_TTL */
+  uint32_t exch_off, exch_len; /* kind 1: exchange name.   kind 0: the method frame's payload */
+  uint32_t key_off, key_len;   /* kind 1: routing key.     kind 0: class id, method id */
+  uint32_t hdr_tbl_off, hdr_tbl_len; /* contents of the `headers` field table (after its length word) */
+  uint32_t seg;
+  uint16_t channel;
+  uint8_t kind;         /* 1 = Basic.Publish, decoded;  0 = any other method, handed back undecoded */
+  uint8_t flags;        /* CHQ_PUB_* */
+} chq_publish_rec;      /* 64 bytes */
+enum {
+  CHQ_PUB_MANDATORY = 1, CHQ_PUB_IMMEDIATE = 2,
+  CHQ_PUB_PERSIST = 4,      /* deliveryMode == 2 */
+  CHQ_PUB_HAS_TTL = 8, CHQ_PUB_HAS_HEADERS = 16,
+  CHQ_PUB_HAS_PROPS = 32    /* a content header was decoded */
+};
+/* host buffers (H2D, kernels, D2H inside); at most 4 GiB per call */
+int32_t chq_decode(const uint8_t* bytes, uint64_t len, const uint64_t* seg_offsets, uint32_t n_seg, chq_publish_rec* recs,
+                   uint64_t recs_cap, uint64_t* n_recs, uint64_t* seg_consumed, int32_t* seg_err, uint64_t* seg_err_off);
+/* device buffers, asynchronous on `stream`; *d_status = CHQ_OK or CHQ_E_OVERFLOW (more commands than recs_cap) */
+int32_t chq_decode_device(const uint8_t* d_bytes, uint64_t len, const uint64_t* d_seg_offsets, uint32_t n_seg,
+                          chq_publish_rec* d_recs, uint64_t recs_cap, uint64_t* d_n_recs, uint64_t* d_seg_consumed,
+                          int32_t* d_seg_err, uint64_t* d_seg_err_off, int32_t* d_status, void* stream);
+/* routing keys of the Basic.Publish records, compacted on the device (order not preserved: d_rec_index[j]
+ * names the record key j came from) — the input of chq_route_keys_device */
+int32_t chq_publish_keys_device(const chq_publish_rec* d_recs, const uint64_t* d_n_recs, uint64_t recs_cap,
+                                uint32_t* d_key_off, uint32_t* d_key_len, uint32_t* d_rec_index, uint32_t* d_n_pub,
+                                void* stream);
+/* chq_route_device for keys scattered inside a byte batch: key i = d_bytes[d_key_off[i] .. + d_key_len[i]) */
+int32_t chq_route_keys_device(chq_table* t, const uint8_t* d_bytes, const uint32_t* d_key_off, const uint32_t* d_key_len,
+                              uint32_t n, uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap,
+                              uint8_t* d_any_durable, uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream);
+
 /* pinned host memory for callers that want zero-copy staging (JNA: new Pointer(addr)) */
 int32_t chq_host_alloc(void** p, uint64_t bytes);
 int32_t chq_host_free(void* p);

@@ -88,6 +88,37 @@ def pair_match(mode, pattern, key):
     return lib().orc_pair_match(mode, p, len(p), k, len(k))
 
 
+REC_DTYPE = np.dtype([  # mirrors chq_publish_rec (oracle/amqp_decode.cpp Rec)
+    ("method_off", "<u8"), ("body_off", "<u8"), ("body_size", "<u8"), ("ttl", "<i8"),
+    ("exch_off", "<u4"), ("exch_len", "<u4"), ("key_off", "<u4"), ("key_len", "<u4"),
+    ("hdr_tbl_off", "<u4"), ("hdr_tbl_len", "<u4"), ("seg", "<u4"), ("channel", "<u2"), ("kind", "u1"), ("flags", "u1"),
+])
+
+
+def decode(data, seg_offsets, chunk=0):
+    """Restated FrameParser + CommandAssembler + property readers over n_seg connection segments, each fed to
+    its own parser in chunks of `chunk` bytes (0 = all at once) -> (recs, seg_consumed, seg_err, seg_err_off)."""
+    L = lib()
+    L.orc_decode.restype = C.c_int
+    L.orc_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_uint64,
+                             C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p, C.c_void_p]
+    data = np.ascontiguousarray(data, dtype=np.uint8)
+    seg = np.ascontiguousarray(seg_offsets, dtype=np.uint64)
+    n_seg = len(seg) - 1
+    cap = len(data) // 12 + n_seg + 1
+    recs = np.zeros(cap, dtype=REC_DTYPE)
+    n = C.c_uint64(0)
+    consumed = np.zeros(max(n_seg, 1), dtype=np.uint64)
+    err = np.zeros(max(n_seg, 1), dtype=np.int32)
+    err_off = np.zeros(max(n_seg, 1), dtype=np.uint64)
+    buf = data if data.size else np.zeros(1, dtype=np.uint8)
+    rc = L.orc_decode(buf.ctypes.data, seg.ctypes.data, n_seg, chunk, recs.ctypes.data, cap, C.byref(n), consumed.ctypes.data,
+                      err.ctypes.data, err_off.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("oracle decode: record capacity")
+    return recs[: n.value].copy(), consumed[:n_seg], err[:n_seg], err_off[:n_seg]
+
+
 class Oracle:
     """One exchange's matcher, restated from the reference (trait QueueMatcher, QueueMatcher.scala:11-27)."""
 
