@@ -357,6 +357,15 @@ int32_t chq_unbind_queue(chq_table* t, const uint8_t* queue, uint32_t queue_len)
   return t->host.unbind_queue(std::string_view((const char*)queue, queue_len));
 }
 
+int32_t chq_declare_queues(chq_table* t, const uint8_t* queues_blob, const uint32_t* queue_offsets, uint32_t n) {
+  if (!t || (n && (!queues_blob || !queue_offsets))) return fail(CHQ_E_ARG, "chq_declare_queues: bad argument");
+  std::lock_guard<std::mutex> g(t->mu);
+  t->committed = t->compiled = false;
+  for (uint32_t i = 0; i < n; ++i)
+    t->host.declare_queue(std::string_view((const char*)queues_blob + queue_offsets[i], queue_offsets[i + 1] - queue_offsets[i]));
+  return CHQ_OK;
+}
+
 int32_t chq_commit(chq_table* t) {
   if (!t) return fail(CHQ_E_ARG, "chq_commit: bad argument");
   std::lock_guard<std::mutex> g(t->mu);
@@ -597,6 +606,63 @@ int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const 
   CU(launch_finish(p.ctrl, d_status, st));
   t->n_batches++;
   t->n_messages += n;
+  return CHQ_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// binding-slice sharding: union of the per-slice results of one batch (after the all-gather)
+// ---------------------------------------------------------------------------------------------
+namespace {
+Workspace g_merge_ws[64];
+}
+
+int32_t chq_merge_slices_device(int32_t device, const uint32_t* d_slice_offsets, const uint32_t* d_slice_ids, uint64_t slice_cap,
+                                const uint8_t* d_slice_durable, uint32_t n_slices, uint32_t n, uint32_t* d_offsets,
+                                uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable, uint64_t* d_total,
+                                int32_t* d_status, void* stream) {
+  if (device < 0 || device >= 64 || !d_slice_offsets || !d_slice_ids || !d_slice_durable || !d_offsets || !d_any_durable ||
+      !d_total || !d_status || n_slices == 0 || n_slices > (uint32_t)kRouteSlots)
+    return fail(CHQ_E_ARG, "chq_merge_slices_device: bad argument (1..8 slices)");
+  if ((uint64_t)n_slices * slice_cap > 0xFFFFFFFFull) return fail(CHQ_E_ARG, "chq_merge_slices_device: gathered ids exceed 2^32-1");
+  CU(cudaSetDevice(device));
+  Workspace& ws = g_merge_ws[device];
+  cudaStream_t st = (cudaStream_t)stream;
+  const uint32_t n_tiles = (n + kRouteThreads - 1) / kRouteThreads;
+  int rc;
+  if ((rc = ws.state.ensure((size_t)n_tiles + 2))) return rc;
+  if ((rc = ws.scratch.ensure(ws.scratch_want))) return rc;
+  CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + 2) * sizeof(uint64_t), st));
+  if (n == 0) {
+    CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
+    CU(cudaMemsetAsync(d_total, 0, sizeof(uint64_t), st));
+    CU(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+    return CHQ_OK;
+  }
+  cudaDeviceProp prop{};
+  static int sms[64] = {};
+  if (!sms[device]) { CU(cudaGetDeviceProperties(&prop, device)); sms[device] = prop.multiProcessorCount; }
+  RouteParams p{};
+  p.tv.qlist = d_slice_ids;
+  p.tv.wstride = 4;
+  p.n = n;
+  p.n_tiles = n_tiles;
+  p.offsets = d_offsets;
+  p.ids = d_queue_ids;
+  p.ids_cap = ids_cap;
+  p.durable = d_any_durable;
+  p.total = d_total;
+  p.ctrl = reinterpret_cast<uint32_t*>(ws.state.p);
+  p.tile_state = ws.state.p + 2;
+  p.scratch = ws.scratch.p;
+  p.scratch_cap = ws.scratch.cap;
+  p.max_slots = kRouteSlots;
+  p.max_small = kRouteSmall;
+  p.slice_offsets = d_slice_offsets;
+  p.slice_durable = d_slice_durable;
+  p.n_slices = n_slices;
+  p.slice_cap = slice_cap;
+  CU(launch_route(p, sms[device], st));
+  CU(launch_finish(p.ctrl, d_status, st));
   return CHQ_OK;
 }
 

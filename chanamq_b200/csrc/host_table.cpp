@@ -96,6 +96,7 @@ void HostTable::compile(CompiledTable& out) const {
   {
     std::set<std::string_view> q;
     for (auto& t : live_) q.insert(std::get<1>(t));
+    for (auto& d : declared_) q.insert(d);
     out.queue_names.assign(q.begin(), q.end());
   }
   std::unordered_map<std::string_view, uint32_t> qid;

@@ -44,6 +44,9 @@ class HostTable {
   int bind(std::string_view key, std::string_view queue, bool durable);
   int unbind(std::string_view key, std::string_view queue, bool durable);
   int unbind_queue(std::string_view queue);
+  // a queue that takes part in the id numbering although nothing is bound to it HERE (binding-slice
+  // sharding: every GPU numbers the queues of the whole exchange, so ids agree across slices)
+  void declare_queue(std::string_view queue) { declared_.emplace(queue); }
   void compile(CompiledTable& out) const;
   size_t size() const { return live_.size(); }
   int type() const { return type_; }
@@ -54,6 +57,7 @@ class HostTable {
   int type_, mode_;
   // the matcher holds a SET of (pattern, queue, durable) triples (QueueMatcher.scala:443-446)
   std::set<std::tuple<std::string, std::string, bool>> live_;
+  std::set<std::string> declared_;
 };
 
 }  // namespace chq

@@ -159,6 +159,37 @@ __device__ uint32_t warp_fallback(const RouteParams& p, const uint32_t* __restri
   return cnt;
 }
 
+// Slow path when the lists are already known (lane j < k holds list j): append, sort, de-duplicate in
+// the global scratch arena.
+__device__ uint32_t warp_fallback_lists(const RouteParams& p, uint32_t my_off, uint32_t my_len, int k, int lane, uint64_t* scr_off) {
+  uint32_t total = lane < k ? my_len : 0;
+#pragma unroll
+  for (int d = 16; d; d >>= 1) total += __shfl_xor_sync(kFull, total, d);
+  *scr_off = 0;
+  if (total == 0) return 0;
+  uint32_t np = 32;
+  while (np < total) np <<= 1;
+  unsigned long long got = 0;
+  if (lane == 0) got = atomicAdd(reinterpret_cast<unsigned long long*>(p.ctrl + kCtrlScratchLo), (unsigned long long)np);
+  const uint64_t base = __shfl_sync(kFull, got, 0);
+  if (base + np > p.scratch_cap) {
+    if (lane == 0) atomicOr(p.ctrl + kCtrlStatus, kStatusScratch);
+    return 0;
+  }
+  uint32_t wpos = 0;
+  for (int j = 0; j < k; ++j) {
+    const uint32_t o = __shfl_sync(kFull, my_off, j), l = __shfl_sync(kFull, my_len, j);
+    for (uint32_t i = lane; i < l; i += 32) p.scratch[base + wpos + i] = __ldg(p.tv.qlist + o + i);
+    wpos += l;
+  }
+  for (uint32_t i = total + lane; i < np; i += 32) p.scratch[base + i] = kNone;
+  __syncwarp();
+  warp_bitonic_sort(p.scratch + base, np, lane);
+  const uint32_t cnt = warp_unique(p.scratch + base, total, lane);
+  *scr_off = base;
+  return cnt;
+}
+
 }  // namespace
 
 __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RouteParams p) {
@@ -183,8 +214,9 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
     // ---- phase A: one thread per message: probe every compatible shape -------------------
     uint32_t k = 0, ub = 0, mxlen = 0, flags = 0, cnt = 0, nw = 0;
     const uint32_t* row = p.wid + (size_t)m * tv.wstride;
-    if (m < p.n) nw = p.nwords[m];
+    if (m < p.n && !p.slice_offsets) nw = p.nwords[m];
     bool overflow = false;  // more tag hits than candidate slots: the slow path re-probes
+    if (p.slice_offsets) nw = m < p.n ? 1u : 0u;
     if (nw > 0 && !(p.debug & 2u)) {
       auto record = [&](const GroupRec& rec) {
         if (k < p.max_slots) { sm.loff[k][tid] = rec.list_off; sm.llen[k][tid] = rec.list_len; }
@@ -193,7 +225,21 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
         mxlen = max(mxlen, rec.list_len);
         flags |= rec.flags;
       };
-      if (tv.exchange_type == 1 /* fanout */) {
+      if (p.slice_offsets) {  // merge of per-slice results: the lists are given, nothing to probe
+        for (uint32_t r = 0; r < p.n_slices; ++r) {
+          const uint32_t* so = p.slice_offsets + (size_t)r * (p.n + 1) + m;
+          const uint32_t a = __ldg(so), e = __ldg(so + 1);
+          if (e > a) {
+            GroupRec rec{};
+            rec.list_off = (uint32_t)(r * p.slice_cap + a);
+            rec.list_len = e - a;
+            rec.flags = kShared | (__ldg(p.slice_durable + (size_t)r * p.n + m) ? kAnyDurable : 0);
+            record(rec);
+          } else if (__ldg(p.slice_durable + (size_t)r * p.n + m)) {
+            flags |= kAnyDurable;
+          }
+        }
+      } else if (tv.exchange_type == 1 /* fanout */) {
         if (tv.fanout_group != kNone) record(load_group(tv, tv.fanout_group));
       } else {
         KeyCtx kctx;
@@ -230,7 +276,16 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
       const uint32_t mm = tile * kRouteThreads + warp * 32 + src;
       uint64_t so;
       uint32_t fl;
-      const uint32_t c = warp_fallback(p, p.wid + (size_t)mm * tv.wstride, __shfl_sync(kFull, nw, src), lane, &so, &fl);
+      uint32_t c;
+      if (p.slice_offsets) {  // lists are in shared memory (at most n_slices <= kRouteSlots of them)
+        const int kk = __shfl_sync(kFull, k, src);
+        uint32_t o = 0, l = 0;
+        if (lane < kk) { o = sm.loff[lane][warp * 32 + src]; l = sm.llen[lane][warp * 32 + src]; }
+        fl = __shfl_sync(kFull, flags, src);
+        c = warp_fallback_lists(p, o, l, kk, lane, &so);
+      } else {
+        c = warp_fallback(p, p.wid + (size_t)mm * tv.wstride, __shfl_sync(kFull, nw, src), lane, &so, &fl);
+      }
       if (lane == src) {
         cnt = c;
         flags = fl;

@@ -30,6 +30,12 @@ struct RouteParams {
   uint32_t* scratch;         // slow-path arena
   uint64_t scratch_cap;      // in ids
   uint32_t max_slots, max_small;
+  // slice-merge mode (binding-slice sharding): instead of probing a table, message m's lists are slice r's
+  // ids slice_ids[r * slice_cap + slice_offsets[r * (n+1) + m] ...] for r < n_slices; tv.qlist = slice_ids
+  const uint32_t* slice_offsets;   // null = normal routing
+  const uint8_t* slice_durable;    // [n_slices][n]
+  uint32_t n_slices;
+  uint64_t slice_cap;
   uint32_t debug;            // experiment switches (env CHQ_DEBUG): 1 = skip phase B, 2 = skip probing
 };
 

@@ -139,6 +139,20 @@ int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const 
                                 uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,
                                 uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream);
 
+/* ---- binding-slice sharding (BASELINE.json configs[3]: binding i lives on GPU i mod G; every GPU routes ALL
+ *      keys against its slice; the per-slice lists are all-gathered and merged).  No counterpart in the
+ *      reference (one exchange = one actor there, entity/ExchangeEntity.scala:107).
+ *      chq_declare_queues makes queue names count for the id numbering of a table although nothing is bound
+ *      to them on this GPU, so that every slice numbers the whole exchange's queues identically. ---- */
+int32_t chq_declare_queues(chq_table* t, const uint8_t* queues_blob, const uint32_t* queue_offsets, uint32_t n);
+/* Union, per message, of n_slices (<= 8) CSR results of the same n keys, laid out as the all-gather leaves
+ * them: offsets [n_slices][n+1], ids [n_slices][slice_cap], any_durable [n_slices][n].  Asynchronous on
+ * `stream`; result and status exactly as chq_route_device. */
+int32_t chq_merge_slices_device(int32_t device, const uint32_t* d_slice_offsets, const uint32_t* d_slice_ids, uint64_t slice_cap,
+                                const uint8_t* d_slice_durable, uint32_t n_slices, uint32_t n, uint32_t* d_offsets,
+                                uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable, uint64_t* d_total,
+                                int32_t* d_status, void* stream);
+
 /* ---- decode seam: FrameParser.onReceive (chana-mq-base/.../engine/FrameParser.scala:78-158) +
  *      CommandAssembler.onReceive (.../engine/CommandAssembler.scala:56-130) + Basic.Publish arguments
  *      (.../method/Basic.scala:45) + BasicProperties.readFrom (.../model/BasicProperties.scala:42-96) + the
