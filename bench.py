@@ -38,8 +38,8 @@ N_BATCHES = 10
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--bindings", type=int, default=1_000_000)
     ap.add_argument("--batch", type=int, default=1 << 20)
@@ -47,7 +47,7 @@ def parse():
                     help="compat = the reference's semantics ('#' is a word); spec = AMQP '#' wildcard")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=100_000)
-    ap.add_argument("--ref-sample", type=int, default=0, help="keys per reference-arm step (0 = 12 500 x threads)")
+    ap.add_argument("--ref-sample", type=int, default=0, help="keys per reference-arm step (0 = sized from a pilot so that the run takes about 75 s)")
     return ap.parse_args()
 
 
@@ -113,13 +113,20 @@ def make_table_inputs(a):
 # --------------------------------------------------------------------------------------------
 # reference arm / cpu_baseline: the C++ restatement of the reference's TrieMatcher (oracle/)
 # --------------------------------------------------------------------------------------------
-def cpu_route_rate(a, w, binds, n_keys, threads, steps, warmup, stream0=1000):
+def cpu_route_rate(a, w, binds, n_keys, threads, steps, warmup, stream0=1000, budget_s=None):
+    """n_keys per step; with budget_s the per-step sample is sized from a pilot so the whole run takes ~budget_s"""
     from oracle import pyoracle as po
 
     o = po.Oracle(po.TOPIC, po.COMPAT if a.mode == "compat" else po.SPEC, inplace=True)
     t0 = time.perf_counter()
     assert o.bind_many(*binds) == 0
     build_s = time.perf_counter() - t0
+    if budget_s:
+        blob, off = w.keys(2000 * threads, stream=stream0 - 1)
+        t0 = time.perf_counter()
+        o.route_packed(blob, off, threads)
+        pilot_rate = 2000 * threads / (time.perf_counter() - t0)
+        n_keys = int(min(1 << 20, max(2000, pilot_rate * budget_s / (steps + warmup))))
     secs, ids = [], 0
     for s in range(warmup + steps):
         blob, off = w.keys(n_keys, stream=stream0 + s)
@@ -129,16 +136,16 @@ def cpu_route_rate(a, w, binds, n_keys, threads, steps, warmup, stream0=1000):
         if s >= warmup:
             secs.append(dt)
             ids += len(o_ids)
-    return n_keys * steps / sum(secs), sum(secs) / steps, build_s, ids / max(1, n_keys * steps)
+    return n_keys * steps / sum(secs), sum(secs) / steps, build_s, ids / max(1, n_keys * steps), n_keys
 
 
 def run_reference(a, rank):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    n_keys = a.ref_sample or 12_500 * threads
     w, binds = make_table_inputs(a)
-    rate, per_step, build_s, mbar = cpu_route_rate(a, w, binds, n_keys, threads, a.steps, a.warmup)
+    rate, per_step, build_s, mbar, n_keys = cpu_route_rate(a, w, binds, a.ref_sample, threads, a.steps, a.warmup,
+                                                           budget_s=None if a.ref_sample else 75.0)
     sample = "%d keys per step x %d steps on %d threads (keys sharded over a read-only trie); trie build %.1f s not timed" % (
         n_keys, a.steps, threads, build_s)
     print(json.dumps({
@@ -234,7 +241,6 @@ def run_ours(a, rank, world, local_rank):
     dev_ms = e0.elapsed_time(e1)
     launches = L.chq_kernel_launches() - launches0
     tok_ms, route_ms, prof_n = m.profile(False)
-    clocks = sampler.stop()
     tot = d_tot.cpu().numpy().reshape(N_BATCHES, 2)
     used = sorted({(a.warmup + i) % N_BATCHES for i in range(a.steps)} | {i % N_BATCHES for i in range(a.warmup)})
     if any((int(tot[b, 1]) & 0xFFFFFFFF) != 0 for b in used):
@@ -267,6 +273,8 @@ def run_ours(a, rank, world, local_rank):
     chk = e2e_run(a.steps, a.warmup)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()  # sampled from the start of the device-timed region to the end of the end-to-end one
+    clocks["window"] = "device-resident + end-to-end timed regions"
     h2d = int(np.mean([hb.numel() + ho.numel() * 4 for hb, ho in host]))
     d2h = int((n + 1) * 4 + 2 * n + 16 + ids_per_batch * 4)
 
@@ -314,7 +322,7 @@ def run_ours(a, rank, world, local_rank):
                          "tokenize_ms": tok_ms / max(1, prof_n), "kernel_share_of_step": route_ms / dev_ms if world == 1 else None},
         }
         if world == 1 and not a.no_cpu_baseline:
-            rate, per_step, cbuild, cm = cpu_route_rate(a, w, binds, a.cpu_sample, 1, 1, 0, stream0=0)
+            rate, per_step, cbuild, cm, _ = cpu_route_rate(a, w, binds, a.cpu_sample, 1, 1, 0, stream0=0)
             out["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
                                    "sample": "%d keys of batch 0 on 1 thread (one exchange = one actor = one thread in the "
                                              "reference, ExchangeEntity.scala:107), %.1f s; trie build %.1f s not timed; "
