@@ -49,6 +49,7 @@ def load_library():
         "chq_table_create": (i32, [C.POINTER(vp), i32, i32, i32]),
         "chq_table_destroy": (i32, [vp]),
         "chq_bind": (i32, [vp, C.c_char_p, u32, C.c_char_p, u32, u8]),
+        "chq_bind_args": (i32, [vp, C.c_char_p, u32, C.c_char_p, u32, u8, C.c_char_p, u32]),
         "chq_bind_many": (i32, [vp, vp, vp, vp, vp, vp, u32]),
         "chq_unbind": (i32, [vp, C.c_char_p, u32, C.c_char_p, u32, u8]),
         "chq_unbind_queue": (i32, [vp, C.c_char_p, u32]),

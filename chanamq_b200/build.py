@@ -22,7 +22,7 @@ def _newer(target, sources):
 
 def build_product(force=False, verbose=False):
     out = os.path.join(HERE, "libchanagpu.so")
-    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "abi.cu", "decode.cu", "host_table.cpp")]
+    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "abi.cu", "decode.cu", "headers.cu", "host_table.cpp", "host_headers.cpp")]
     deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "chanamq_gpu.h")]
     if not force and not _newer(out, deps):
         return out

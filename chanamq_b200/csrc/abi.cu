@@ -3,6 +3,7 @@
 // kernels.cu; there is no CPU fallback — a CUDA failure is returned as CHQ_E_CUDA.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -83,13 +84,19 @@ struct Workspace {
   DevBuf<uint8_t> nwords;
   DevBuf<uint64_t> state;   // [0..1] = control words, [2..] = per-tile scan state
   DevBuf<uint32_t> scratch;
+  DevBuf<uint32_t> desc_k;      // headers exchange: matched lists per message (k_headers_match -> k_route)
+  DevBuf<uint32_t> desc_start;
+  DevBuf<uint8_t> desc_flags;
+  DevBuf<uint2> desc_lists;
   size_t scratch_want = 16u << 20;
+  size_t desc_want = 1u << 20;  // descriptor arena (grown after CHQ_E_SCRATCH)
   // optional per-kernel timing (chq_profile): events on the launching stream around each kernel
   static constexpr int kProfRing = 256;
   cudaEvent_t ev[kProfRing][3] = {};
   int prof_n = 0;
   void release() {
     wid.release(); nwords.release(); state.release(); scratch.release();
+    desc_k.release(); desc_start.release(); desc_flags.release(); desc_lists.release();
     for (auto& e : ev) for (auto& x : e) if (x) { cudaEventDestroy(x); x = nullptr; }
     prof_n = 0;
   }
@@ -138,6 +145,11 @@ struct chq_table {
   DevBuf<uint32_t> d_slot_group;
   DevBuf<Group> d_groups;
   DevBuf<uint32_t> d_lits, d_rems, d_qlist;
+  DevBuf<DictSlot> d_vdict;
+  DevBuf<uint8_t> d_vdict_bytes;
+  DevBuf<uint32_t> d_presence, d_all_atoms;
+  DevBuf<AtomRec> d_atoms;
+  DevBuf<AllGroup> d_all_groups;
   TableView tv{};
   RouteSlot slots[CHQ_SLOTS];
   Workspace dev_ws;  // for chq_route_device
@@ -169,8 +181,29 @@ int upload_table(chq_table* t) {
   if ((rc = t->d_lits.upload(c.lits.data(), c.lits.size(), st))) return rc;
   if ((rc = t->d_rems.upload(c.rems.data(), c.rems.size(), st))) return rc;
   if ((rc = t->d_qlist.upload(c.qlist.data(), c.qlist.size(), st))) return rc;
+  if (c.headers_mode) {
+    if ((rc = t->d_vdict.upload(c.vdict.data(), c.vdict.size(), st))) return rc;
+    if ((rc = t->d_vdict_bytes.upload(c.vdict_bytes.data(), c.vdict_bytes.size(), st))) return rc;
+    if ((rc = t->d_presence.upload(c.presence_atom.data(), c.presence_atom.size(), st))) return rc;
+    if ((rc = t->d_all_atoms.upload(c.all_atoms.data(), c.all_atoms.size(), st))) return rc;
+    if ((rc = t->d_atoms.upload(c.atoms.data(), c.atoms.size(), st))) return rc;
+    if ((rc = t->d_all_groups.upload(c.all_groups.data(), c.all_groups.size(), st))) return rc;
+  }
   CU(cudaStreamSynchronize(st));
   TableView& v = t->tv;
+  v = TableView{};
+  if (c.headers_mode) {
+    v.vdict = t->d_vdict.p;
+    v.vdict_bytes = t->d_vdict_bytes.p;
+    v.vdict_mask = (uint32_t)c.vdict.size() - 1;
+    v.presence_atom = t->d_presence.p;
+    v.atoms = t->d_atoms.p;
+    v.all_groups = t->d_all_groups.p;
+    v.all_atoms = t->d_all_atoms.p;
+    v.always_off = c.always_off;
+    v.always_len = c.always_len;
+    v.always_flags = c.always_flags;
+  }
   v.dict = t->d_dict.p;
   v.dict_bytes = t->d_dict_bytes.p;
   v.dict_mask = (uint32_t)c.dict.size() - 1;
@@ -197,12 +230,20 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
                   uint32_t* d_offsets, uint32_t* d_ids, uint64_t ids_cap, uint8_t* d_durable, uint8_t* d_err,
                   uint64_t* d_total, int32_t* d_status, cudaStream_t st) {
   const uint32_t n_tiles = (n + kRouteThreads - 1) / kRouteThreads;
+  const bool headers = t->ct.headers_mode;  // d_blob/d_off/d_klen then describe the messages' headers tables
   int rc;
-  if ((rc = ws.wid.ensure((size_t)n * t->tv.wstride + 4))) return rc;
-  if ((rc = ws.nwords.ensure((size_t)n + 1))) return rc;
-  if ((rc = ws.state.ensure((size_t)n_tiles + 2))) return rc;
+  if (headers) {
+    if ((rc = ws.desc_k.ensure((size_t)n + 1))) return rc;
+    if ((rc = ws.desc_start.ensure((size_t)n + 1))) return rc;
+    if ((rc = ws.desc_flags.ensure((size_t)n + 1))) return rc;
+    if ((rc = ws.desc_lists.ensure(std::max<size_t>((size_t)n * kHeaderListsPerMessage, ws.desc_want)))) return rc;
+  } else {
+    if ((rc = ws.wid.ensure((size_t)n * t->tv.wstride + 4))) return rc;
+    if ((rc = ws.nwords.ensure((size_t)n + 1))) return rc;
+  }
+  if ((rc = ws.state.ensure((size_t)n_tiles + 3))) return rc;
   if ((rc = ws.scratch.ensure(ws.scratch_want))) return rc;
-  CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + 2) * sizeof(uint64_t), st));
+  CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + 3) * sizeof(uint64_t), st));
   if (n == 0) {
     CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
     CU(cudaMemsetAsync(d_total, 0, sizeof(uint64_t), st));
@@ -217,7 +258,12 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
       if (!pe[i]) CU(cudaEventCreate(&pe[i]));
     CU(cudaEventRecord(pe[0], st));
   }
-  if (d_klen) CU(launch_tokenize_keys(d_blob, d_off, d_klen, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
+  if (headers)
+    CU(launch_headers_match(d_blob, d_off, d_klen, n, t->tv, ws.desc_k.p, ws.desc_start.p, ws.desc_flags.p, ws.desc_lists.p,
+                            (uint32_t)std::min<size_t>(ws.desc_lists.cap, 0xFFFFFFFFu),
+                            reinterpret_cast<uint32_t*>(ws.state.p + n_tiles + 2), reinterpret_cast<uint32_t*>(ws.state.p) + kCtrlStatus,
+                            d_err, st));
+  else if (d_klen) CU(launch_tokenize_keys(d_blob, d_off, d_klen, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
   else CU(launch_tokenize(d_blob, d_off, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
   if (pe) CU(cudaEventRecord(pe[1], st));
   RouteParams p{};
@@ -237,6 +283,7 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   p.scratch_cap = ws.scratch.cap;
   p.max_slots = t->max_slots;
   p.max_small = t->max_small;
+  if (headers) { p.desc_k = ws.desc_k.p; p.desc_start = ws.desc_start.p; p.desc_flags = ws.desc_flags.p; p.desc_lists = ws.desc_lists.p; }
   { const char* dbg = getenv("CHQ_DEBUG"); p.debug = dbg ? (uint32_t)atoi(dbg) : 0u; }
   CU(launch_route(p, t->n_sms, st));
   if (pe) CU(cudaEventRecord(pe[2], st));
@@ -314,6 +361,8 @@ int32_t chq_table_destroy(chq_table* t) {
   for (auto& s : t->slots) s.release();
   t->dev_ws.release();
   t->d_dict.release(); t->d_dict_bytes.release(); t->d_shapes.release(); t->d_exact.release();
+  t->d_vdict.release(); t->d_vdict_bytes.release(); t->d_presence.release(); t->d_all_atoms.release();
+  t->d_atoms.release(); t->d_all_groups.release();
   t->d_tags.release(); t->d_slot_group.release(); t->d_groups.release(); t->d_lits.release(); t->d_rems.release(); t->d_qlist.release();
   delete t;
   return CHQ_OK;
@@ -325,6 +374,17 @@ int32_t chq_bind(chq_table* t, const uint8_t* key, uint32_t key_len, const uint8
   std::lock_guard<std::mutex> g(t->mu);
   t->committed = t->compiled = false;
   return t->host.bind(std::string_view((const char*)key, key_len), std::string_view((const char*)queue, queue_len), durable != 0);
+}
+
+int32_t chq_bind_args(chq_table* t, const uint8_t* key, uint32_t key_len, const uint8_t* queue, uint32_t queue_len,
+                      uint8_t durable, const uint8_t* args_table, uint32_t args_len) {
+  if (!t || (!key && key_len) || (!queue && queue_len) || (!args_table && args_len)) return fail(CHQ_E_ARG, "chq_bind_args: bad argument");
+  std::lock_guard<std::mutex> g(t->mu);
+  t->committed = t->compiled = false;
+  int rc = t->host.bind(std::string_view((const char*)key, key_len), std::string_view((const char*)queue, queue_len), durable != 0,
+                        std::string_view((const char*)args_table, args_len));
+  if (rc == CHQ_E_ARG) return fail(rc, "chq_bind_args: malformed arguments table");
+  return rc;
 }
 
 int32_t chq_bind_many(chq_table* t, const uint8_t* keys_blob, const uint32_t* key_offsets, const uint8_t* queues_blob,
@@ -461,7 +521,7 @@ int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
     // grow what was too small and run the batch again (inputs are still on the device)
     CU(cudaStreamSynchronize(s.st));
     if (status == CHQ_E_OVERFLOW) { if ((rc = s.d_ids.ensure(total + 1024))) return rc; }
-    else { s.ws.scratch_want = s.ws.scratch.cap * 4; }
+    else { s.ws.scratch_want = s.ws.scratch.cap * 4; s.ws.desc_want = std::max<size_t>(s.ws.desc_lists.cap, 1) * 4; }
     if ((rc = slot_launch(t, s))) return rc;
   }
   const uint64_t total = s.r_total.p[0];
@@ -480,8 +540,12 @@ int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
 
 int32_t chq_route(chq_table* t, const uint8_t* keys_blob, const uint32_t* key_offsets, uint32_t n,
                   const uint8_t* headers_blob, const uint32_t* headers_offsets, chq_result* out) {
-  (void)headers_blob;
-  (void)headers_offsets;
+  if (t && t->host.type() == CHQ_HEADERS && t->host.mode() == CHQ_MODE_SPEC) {
+    // x-match routing: the messages' headers tables are the input, the routing keys play no part
+    if (n && (!headers_blob || !headers_offsets)) return fail(CHQ_E_ARG, "chq_route: a headers exchange needs headers_blob/headers_offsets");
+    keys_blob = headers_blob;
+    key_offsets = headers_offsets;
+  }
   int rc = chq_route_submit(t, 0, keys_blob, key_offsets, n);
   if (rc) return rc;
   return chq_route_wait(t, 0, out);

@@ -78,6 +78,24 @@ struct DictSlot {         // 32 B: one interned pattern word
   uint32_t pad;
 };
 
+// ---- headers exchange (SPEC mode; AMQP 0-9-1 x-match all/any — the reference has none, ExchangeEntity.scala:210) ----
+// An ATOM is one thing a binding argument can ask of a message: "field <name> is present" (a void
+// argument) or "field <name> has exactly this typed value".  A message's headers table is turned into
+// the set of atoms it satisfies; an `any` binding matches if one of its atoms is in the set, an `all`
+// binding if every one of its atoms is.
+struct AtomRec {          // 32 B
+  uint32_t any_off, any_len, any_flags;   // queues of the `any` bindings that list this atom (sorted, unique)
+  uint32_t all_begin, all_end;            // `all` groups anchored at this atom (their rarest atom)
+  uint32_t pad[3];
+};
+struct AllGroup {         // 32 B: the `all` bindings with one and the same atom set
+  uint32_t atoms_off, n_atoms;            // into all_atoms (ascending)
+  uint32_t list_off, list_len, flags;
+  uint32_t pad[3];
+};
+constexpr int kMaxHeaderFields = 64;      // known-name fields considered per message
+constexpr int kHeaderListsPerMessage = 16; // descriptor arena = this many matched lists per message on average
+
 // Device view of a committed table (all pointers are device pointers).
 struct TableView {
   const DictSlot* dict;
@@ -101,6 +119,15 @@ struct TableView {
   // fanout = a single always-matching group
   uint32_t exchange_type;
   uint32_t fanout_group;
+  // headers exchange in SPEC mode (null otherwise); field names are interned in dict/dict_bytes
+  const DictSlot* vdict;        // (name id, tag, value bytes) -> atom id; DictSlot.pad = name id << 8 | tag
+  const uint8_t* vdict_bytes;
+  uint32_t vdict_mask;
+  const uint32_t* presence_atom;  // [names + 1]: atom "field present", 0 = nobody asks
+  const AtomRec* atoms;           // [atoms + 1]
+  const AllGroup* all_groups;
+  const uint32_t* all_atoms;
+  uint32_t always_off, always_len, always_flags;  // `all` bindings without arguments: match everything
 };
 
 // --- hashing -------------------------------------------------------------------------------

@@ -38,17 +38,23 @@ int HostTable::check_key(std::string_view key) const {
   return CHQ_OK;
 }
 
-int HostTable::bind(std::string_view key, std::string_view queue, bool durable) {
+bool valid_field_table(std::string_view t);  // host_headers.cpp
+
+int HostTable::bind(std::string_view key, std::string_view queue, bool durable, std::string_view args) {
   int rc = check_key(key);
   if (rc != CHQ_OK) return rc;
-  live_.emplace(std::string(key), std::string(queue), durable);
+  if (!args.empty() && !valid_field_table(args)) return CHQ_E_ARG;
+  live_.emplace(std::string(key), std::string(queue), durable, std::string(args));
   return CHQ_OK;
 }
 
 int HostTable::unbind(std::string_view key, std::string_view queue, bool durable) {
   int rc = check_key(key);
   if (rc != CHQ_OK) return rc;
-  live_.erase(std::make_tuple(std::string(key), std::string(queue), durable));
+  // queueUnbind(queue, routingKey) ignores the arguments (ExchangeEntity.scala:370-382): every variant goes
+  auto it = live_.lower_bound(std::make_tuple(std::string(key), std::string(queue), durable, std::string()));
+  while (it != live_.end() && std::get<0>(*it) == key && std::get<1>(*it) == queue && std::get<2>(*it) == durable)
+    it = live_.erase(it);
   return CHQ_OK;
 }
 
@@ -103,6 +109,10 @@ void HostTable::compile(CompiledTable& out) const {
   qid.reserve(out.queue_names.size() * 2);
   for (uint32_t i = 0; i < out.queue_names.size(); ++i) qid.emplace(out.queue_names[i], i);
 
+  if (type_ == CHQ_HEADERS && mode_ == CHQ_MODE_SPEC) {  // x-match on the arguments; the routing key plays no part
+    compile_headers(out);
+    return;
+  }
   const bool split = (type_ == CHQ_TOPIC || type_ == CHQ_HEADERS);
   const bool spec = (mode_ == CHQ_MODE_SPEC) && split;
 

@@ -28,6 +28,14 @@ struct CompiledTable {
   std::vector<uint32_t> lits, rems, qlist;
   uint32_t wstride = 4;
   uint32_t fanout_group = kNone;
+  // headers exchange, SPEC mode
+  bool headers_mode = false;
+  std::vector<DictSlot> vdict;
+  std::vector<uint8_t> vdict_bytes;
+  std::vector<uint32_t> presence_atom, all_atoms;
+  std::vector<AtomRec> atoms;
+  std::vector<AllGroup> all_groups;
+  uint32_t always_off = 0, always_len = 0, always_flags = 0;
   std::vector<std::string> queue_names;  // id -> name, ascending by bytes
   // statistics for chq_stats / the roofline model
   uint64_t n_bindings = 0, n_heads = 0, pattern_words = 0, n_words = 0;
@@ -41,7 +49,8 @@ class HostTable {
  public:
   HostTable(int exchange_type, int mode) : type_(exchange_type), mode_(mode) {}
   // 0, or a negative chq status (zero-word pattern, key too long)
-  int bind(std::string_view key, std::string_view queue, bool durable);
+  // args = contents of the binding's arguments field table (headers exchanges; empty otherwise)
+  int bind(std::string_view key, std::string_view queue, bool durable, std::string_view args = {});
   int unbind(std::string_view key, std::string_view queue, bool durable);
   int unbind_queue(std::string_view queue);
   // a queue that takes part in the id numbering although nothing is bound to it HERE (binding-slice
@@ -56,7 +65,8 @@ class HostTable {
   int check_key(std::string_view key) const;
   int type_, mode_;
   // the matcher holds a SET of (pattern, queue, durable) triples (QueueMatcher.scala:443-446)
-  std::set<std::tuple<std::string, std::string, bool>> live_;
+  void compile_headers(CompiledTable& out) const;  // host_headers.cpp
+  std::set<std::tuple<std::string, std::string, bool, std::string>> live_;
   std::set<std::string> declared_;
 };
 

@@ -159,6 +159,35 @@ __device__ uint32_t warp_fallback(const RouteParams& p, const uint32_t* __restri
   return cnt;
 }
 
+// Slow path with the lists given as (offset, length) descriptors in global memory.
+__device__ uint32_t warp_fallback_desc(const RouteParams& p, const uint2* __restrict__ desc, uint32_t k, int lane, uint64_t* scr_off) {
+  uint32_t total = 0;
+  for (uint32_t j = 0; j < k; ++j) total += __ldg(desc + j).y;
+  *scr_off = 0;
+  if (total == 0) return 0;
+  uint32_t np = 32;
+  while (np < total) np <<= 1;
+  unsigned long long got = 0;
+  if (lane == 0) got = atomicAdd(reinterpret_cast<unsigned long long*>(p.ctrl + kCtrlScratchLo), (unsigned long long)np);
+  const uint64_t base = __shfl_sync(kFull, got, 0);
+  if (base + np > p.scratch_cap) {
+    if (lane == 0) atomicOr(p.ctrl + kCtrlStatus, kStatusScratch);
+    return 0;
+  }
+  uint32_t wpos = 0;
+  for (uint32_t j = 0; j < k; ++j) {
+    const uint2 d = __ldg(desc + j);
+    for (uint32_t i = lane; i < d.y; i += 32) p.scratch[base + wpos + i] = __ldg(p.tv.qlist + d.x + i);
+    wpos += d.y;
+  }
+  for (uint32_t i = total + lane; i < np; i += 32) p.scratch[base + i] = kNone;
+  __syncwarp();
+  warp_bitonic_sort(p.scratch + base, np, lane);
+  const uint32_t cnt = warp_unique(p.scratch + base, total, lane);
+  *scr_off = base;
+  return cnt;
+}
+
 // Slow path when the lists are already known (lane j < k holds list j): append, sort, de-duplicate in
 // the global scratch arena.
 __device__ uint32_t warp_fallback_lists(const RouteParams& p, uint32_t my_off, uint32_t my_len, int k, int lane, uint64_t* scr_off) {
@@ -214,9 +243,9 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
     // ---- phase A: one thread per message: probe every compatible shape -------------------
     uint32_t k = 0, ub = 0, mxlen = 0, flags = 0, cnt = 0, nw = 0;
     const uint32_t* row = p.wid + (size_t)m * tv.wstride;
-    if (m < p.n && !p.slice_offsets) nw = p.nwords[m];
+    if (m < p.n && !p.slice_offsets && !p.desc_k) nw = p.nwords[m];
     bool overflow = false;  // more tag hits than candidate slots: the slow path re-probes
-    if (p.slice_offsets) nw = m < p.n ? 1u : 0u;
+    if (p.slice_offsets || p.desc_k) nw = m < p.n ? 1u : 0u;
     if (nw > 0 && !(p.debug & 2u)) {
       auto record = [&](const GroupRec& rec) {
         if (k < p.max_slots) { sm.loff[k][tid] = rec.list_off; sm.llen[k][tid] = rec.list_len; }
@@ -239,6 +268,17 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
             flags |= kAnyDurable;
           }
         }
+      } else if (p.desc_k) {  // headers exchange: k_headers_match left the lists in global memory
+        const uint32_t kd = __ldg(p.desc_k + m);
+        const uint2* dl = p.desc_lists + __ldg(p.desc_start + m);
+        for (uint32_t j = 0; j < kd; ++j) {
+          const uint2 d = __ldg(dl + j);
+          GroupRec rec{};
+          rec.list_off = d.x;
+          rec.list_len = d.y;
+          record(rec);
+        }
+        flags |= __ldg(p.desc_flags + m);
       } else if (tv.exchange_type == 1 /* fanout */) {
         if (tv.fanout_group != kNone) record(load_group(tv, tv.fanout_group));
       } else {
@@ -277,7 +317,10 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
       uint64_t so;
       uint32_t fl;
       uint32_t c;
-      if (p.slice_offsets) {  // lists are in shared memory (at most n_slices <= kRouteSlots of them)
+      if (p.desc_k) {  // more lists than shared-memory slots: read the descriptors again
+        fl = __shfl_sync(kFull, flags, src);
+        c = warp_fallback_desc(p, p.desc_lists + __ldg(p.desc_start + mm), __shfl_sync(kFull, k, src), lane, &so);
+      } else if (p.slice_offsets) {  // lists are in shared memory (at most n_slices <= kRouteSlots of them)
         const int kk = __shfl_sync(kFull, k, src);
         uint32_t o = 0, l = 0;
         if (lane < kk) { o = sm.loff[lane][warp * 32 + src]; l = sm.llen[lane][warp * 32 + src]; }

@@ -13,6 +13,8 @@ constexpr int kRouteSmall = 512;     // ids (all lists but the longest) a warp m
 
 // control words (device): zeroed before every launch
 constexpr int kCtrlTile = 0, kCtrlStatus = 1, kCtrlScratchLo = 2 /* u64 bump pointer */, kCtrlWords = 4;
+// the headers matcher keeps its descriptor-arena bump pointer in the word after the tile state
+
 constexpr uint32_t kStatusOverflow = 1, kStatusScratch = 2;
 
 struct RouteParams {
@@ -36,6 +38,11 @@ struct RouteParams {
   const uint8_t* slice_durable;    // [n_slices][n]
   uint32_t n_slices;
   uint64_t slice_cap;
+  // descriptor mode (headers exchange): message m's lists are desc_lists[desc_start[m] + j], j < desc_k[m]
+  const uint32_t* desc_k;          // null = not this mode
+  const uint32_t* desc_start;      // message m's descriptors are desc_lists[desc_start[m] ...]
+  const uint8_t* desc_flags;
+  const uint2* desc_lists;
   uint32_t debug;            // experiment switches (env CHQ_DEBUG): 1 = skip phase B, 2 = skip probing
 };
 
@@ -44,6 +51,9 @@ cudaError_t launch_tokenize(const uint8_t* blob, const uint32_t* off, uint32_t n
 cudaError_t launch_tokenize_keys(const uint8_t* bytes, const uint32_t* key_off, const uint32_t* key_len, uint32_t n,
                                  const TableView& tv, int split, uint32_t* wid, uint8_t* nwords, uint8_t* err, cudaStream_t st);
 void note_launches(int n);
+cudaError_t launch_headers_match(const uint8_t* blob, const uint32_t* off, const uint32_t* hlen, uint32_t n, const TableView& tv,
+                                 uint32_t* desc_k, uint32_t* desc_start, uint8_t* desc_flags, uint2* desc_lists, uint32_t arena_cap,
+                                 uint32_t* arena_used, uint32_t* status_word, uint8_t* err, cudaStream_t st);
 cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st);
 cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t st);
 unsigned long long kernel_launches();

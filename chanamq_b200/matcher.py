@@ -105,6 +105,22 @@ class GpuMatcher:
         self._dirty = True
         return rc
 
+    def bind_args(self, key, queue, durable, args_table):
+        """bind with the raw contents of the binding's arguments field table (headers exchanges)"""
+        k, q, a = _b(key), _b(queue), bytes(args_table)
+        rc = self.L.chq_bind_args(self.h, k, len(k), q, len(q), int(durable), a, len(a))
+        self._dirty = True
+        return rc
+
+    def route_headers_packed(self, blob, off, copy=True):
+        """headers exchange: blob/off = the messages' headers tables (field table contents), packed"""
+        self._ensure()
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.uint32)
+        res = ChqResult()
+        check(self.L.chq_route(self.h, None, None, len(off) - 1, blob.ctypes.data, off.ctypes.data, C.byref(res)))
+        return self._result(res, copy)
+
     def unbind(self, key, queue, durable=False):
         k, q = _b(key), _b(queue)
         check(self.L.chq_unbind(self.h, k, len(k), q, len(q), int(durable)))

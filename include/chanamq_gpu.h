@@ -57,6 +57,13 @@ int32_t chq_table_destroy(chq_table* t);
  * Binding an identical (key, queue, durable) triple again is a no-op (engine/QueueMatcher.scala:443-446). */
 int32_t chq_bind(chq_table* t, const uint8_t* key, uint32_t key_len, const uint8_t* queue, uint32_t queue_len,
                  uint8_t durable);
+/* The same with the binding's arguments (Queue.Bind arguments -> ExchangeEntity.QueueBind.arguments,
+ * entity/ExchangeEntity.scala:90): args_table = the CONTENTS of the AMQP field table (after its length word),
+ * typed as on the wire.  Only a CHQ_HEADERS table in CHQ_MODE_SPEC looks at them: x-match = "all" (default)
+ * or "any"; other "x-" names are ignored; a void argument asks for the header's presence, any other for the
+ * same type tag and the same bytes.  A malformed table is CHQ_E_ARG. */
+int32_t chq_bind_args(chq_table* t, const uint8_t* key, uint32_t key_len, const uint8_t* queue, uint32_t queue_len,
+                      uint8_t durable, const uint8_t* args_table, uint32_t args_len);
 /* bulk form of the same call, for replaying the stored binds at start-up (entity/ExchangeEntity.scala:155-157) */
 int32_t chq_bind_many(chq_table* t, const uint8_t* keys_blob, const uint32_t* key_offsets,
                       const uint8_t* queues_blob, const uint32_t* queue_offsets, const uint8_t* durable,
@@ -77,7 +84,9 @@ int32_t chq_queue_name(const chq_table* t, uint32_t queue_id, const uint8_t** na
  *      for a whole Publishs batch.  Message i gets queue_ids[offsets[i] .. offsets[i+1]) — the SET of
  *      queue names over all matching bindings (entity/ExchangeEntity.scala:300), ascending;
  *      any_durable[i] = OR of the matched subscribers' isDurable (entity/ExchangeEntity.scala:302);
- *      err[i] = 1 for a zero-word key, 2 for a key longer than 255 bytes (no queues then). ---- */
+ *      err[i] = 1 for a zero-word key, 2 for a key longer than 255 bytes (no queues then);
+ *      headers exchanges: 3 for a malformed headers table, 4 for more than 64 header fields whose names
+ *      some binding mentions. ---- */
 typedef struct {
   uint32_t n;
   const uint32_t* offsets;   /* n+1 */
@@ -101,7 +110,8 @@ int32_t chq_route_submit(chq_table* t, int32_t slot, const uint8_t* keys_blob, c
 int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out);
 
 /* Device buffers in, device result out, asynchronous on `stream` (a cudaStream_t; NULL = default
- * stream).  d_status receives a chq status word once the stream reaches it; d_total the id count.
+ * stream).  For a CHQ_HEADERS table in CHQ_MODE_SPEC the "keys" are the messages' headers tables (field
+ * table contents), here and in chq_route_keys_device (which takes the hdr_tbl_off / hdr_tbl_len of decode records).  d_status receives a chq status word once the stream reaches it; d_total the id count.
  * d_ids holds ids_cap entries; a larger result sets CHQ_E_OVERFLOW and writes nothing past it. */
 int32_t chq_route_device(chq_table* t, const uint8_t* d_keys_blob, const uint32_t* d_key_offsets, uint32_t n,
                          uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,

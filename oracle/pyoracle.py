@@ -119,6 +119,59 @@ def decode(data, seg_offsets, chunk=0):
     return recs[: n.value].copy(), consumed[:n_seg], err[:n_seg], err_off[:n_seg]
 
 
+class HeadersOracle:
+    """Brute-force x-match all/any over (message, binding) pairs (oracle/headers_spec.cpp; parity unpinned)."""
+
+    def __init__(self):
+        L = self.L = lib()
+        L.orch_new.restype = C.c_void_p
+        L.orch_free.argtypes = [C.c_void_p]
+        L.orch_bind.restype = C.c_int
+        L.orch_bind.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_int, C.c_char_p, C.c_uint32]
+        L.orch_n_queues.restype = C.c_uint32
+        L.orch_n_queues.argtypes = [C.c_void_p]
+        L.orch_queue_name.restype = C.c_int
+        L.orch_queue_name.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32)]
+        L.orch_route.restype = C.c_int64
+        L.orch_route.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
+        for f in (L.orch_offsets, L.orch_ids, L.orch_durable, L.orch_err):
+            f.restype = C.c_void_p
+            f.argtypes = [C.c_void_p]
+        self.h = L.orch_new()
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orch_free(self.h)
+            self.h = None
+
+    def bind(self, queue, durable, args_table):
+        q, a = _b(queue), bytes(args_table)
+        return self.L.orch_bind(self.h, q, len(q), int(durable), a, len(a))
+
+    def queue_names(self):
+        out = []
+        p, n = C.c_void_p(), C.c_uint32()
+        for i in range(self.L.orch_n_queues(self.h)):
+            self.L.orch_queue_name(self.h, i, C.byref(p), C.byref(n))
+            out.append(C.string_at(p, n.value))
+        return out
+
+    def route_packed(self, blob, off):
+        n = len(off) - 1
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.uint32)
+        total = self.L.orch_route(self.h, blob.ctypes.data, off.ctypes.data, n)
+
+        def arr(ptr, count, dt):
+            if count == 0:
+                return np.zeros(0, dtype=dt)
+            buf = (C.c_uint8 * (count * np.dtype(dt).itemsize)).from_address(ptr)
+            return np.frombuffer(buf, dtype=dt, count=count).copy()
+
+        return (arr(self.L.orch_offsets(self.h), n + 1, np.uint32), arr(self.L.orch_ids(self.h), int(total), np.uint32),
+                arr(self.L.orch_durable(self.h), n, np.uint8), arr(self.L.orch_err(self.h), n, np.uint8))
+
+
 class Oracle:
     """One exchange's matcher, restated from the reference (trait QueueMatcher, QueueMatcher.scala:11-27)."""
 

@@ -1,0 +1,168 @@
+"""Headers exchange, x-match all/any (SPEC mode; parity unpinned — the reference has no headers matcher,
+chana-mq-server/.../entity/ExchangeEntity.scala:210).  CPU: the brute-force oracle on the AMQP rule's own
+examples.  GPU: k_headers_match + k_route (descriptor mode) through the C ABI against that oracle, on small
+tables with every field type and on the config-3 shape (8 fields per message, 8 argument slots per binding,
+Zipf template pool), plus COMPAT mode, where a headers exchange routes by key like the reference does."""
+import random
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as po
+from tests import amqp_build as ab
+
+
+def tbl(fields):
+    """field table CONTENTS (no length word) from [(name, tag, value)]"""
+    return ab.table(fields)[4:]
+
+
+def pack(tables):
+    off = np.zeros(len(tables) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum([len(t) for t in tables])
+    blob = np.frombuffer(b"".join(tables) or b"\0", dtype=np.uint8).copy()
+    return blob, off
+
+
+BINDS = [  # (queue, durable, args)
+    ("q_all_ab", False, [("x-match", "S", b"all"), ("a", "S", b"1"), ("b", "I", 2)]),
+    ("q_any_ab", True, [("x-match", "S", b"any"), ("a", "S", b"1"), ("b", "I", 2)]),
+    ("q_default_all", False, [("a", "S", b"1")]),
+    ("q_void", False, [("x-match", "S", b"all"), ("c", "V", None)]),
+    ("q_any_void", False, [("x-match", "S", b"any"), ("c", "V", None), ("zz", "S", b"no")]),
+    ("q_everything", True, [("x-match", "S", b"all")]),
+    ("q_nothing", False, [("x-match", "S", b"any")]),
+    ("q_xignored", False, [("x-match", "S", b"all"), ("x-other", "S", b"whatever"), ("a", "S", b"1")]),
+    ("q_typed", False, [("x-match", "S", b"all"), ("n", "l", 7), ("t", "t", True), ("f", "F", [("in", "I", 1)])]),
+    ("q_dupname", False, [("x-match", "S", b"all"), ("a", "S", b"1"), ("a", "S", b"2")]),
+    ("q_all_ab", False, [("x-match", "S", b"any"), ("d", "S", b"dd")]),  # same queue, second binding
+]
+MSGS = [
+    ([("a", "S", b"1"), ("b", "I", 2)], {"q_all_ab", "q_any_ab", "q_default_all", "q_everything", "q_xignored", "q_dupname"}),
+    ([("a", "S", b"1")], {"q_any_ab", "q_default_all", "q_everything", "q_xignored", "q_dupname"}),
+    ([("b", "I", 2)], {"q_any_ab", "q_everything"}),
+    ([("b", "S", b"2")], {"q_everything"}),                                   # same bytes? no: other type tag
+    ([("a", "S", b"2"), ("a", "S", b"1")], {"q_everything"}),                 # first occurrence of a name counts
+    ([("c", "t", False)], {"q_void", "q_any_void", "q_everything"}),
+    ([], {"q_everything"}),
+    ([("n", "l", 7), ("t", "t", True), ("f", "F", [("in", "I", 1)]), ("d", "S", b"dd")], {"q_typed", "q_everything", "q_all_ab"}),
+    ([("n", "I", 7), ("t", "t", True), ("f", "F", [("in", "I", 1)])], {"q_everything"}),
+]
+
+
+def test_oracle_on_the_rule():
+    o = po.HeadersOracle()
+    for q, d, args in BINDS:
+        assert o.bind(q, d, tbl(args)) == 0
+    names = o.queue_names()
+    off, ids, dur, err = o.route_packed(*pack([tbl(m) for m, _ in MSGS] + [b"\x05abc"]))
+    for i, (_, want) in enumerate(MSGS):
+        assert {names[j].decode() for j in ids[off[i]:off[i + 1]]} == want, i
+    assert err.tolist() == [0] * len(MSGS) + [3] and dur[0] == 1 and dur[3] == 1
+    assert o.bind("q", False, b"\x01a?") == -5
+
+
+def _workload(seed, n_bind, n_msg, n_queues):
+    """config-3 shape: 64 names, values per name, messages = 8 distinct fields from a Zipf template pool"""
+    rng = random.Random(seed)
+    names = ["h%02d" % i for i in range(64)]
+
+    def value(ni):
+        r = rng.random()
+        if r < 0.90:
+            return ("S", ("v%d_%d" % (ni, rng.randrange(40))).encode())
+        if r < 0.94:
+            return ("I", rng.randrange(5))
+        if r < 0.97:
+            return ("t", rng.random() < 0.5)
+        return ("l", rng.randrange(3))
+
+    templates = []
+    for _ in range(300):
+        ns = rng.sample(range(64), 8)
+        templates.append([(names[i],) + value(i) for i in ns])
+    weights = [1.0 / (i + 1) for i in range(len(templates))]
+    binds = []
+    for b in range(n_bind):
+        q = "q%05d" % rng.randrange(n_queues)
+        if rng.random() < 0.5:
+            args = [("x-match", "S", b"any")] + [(names[i],) + value(i) for i in rng.sample(range(64), 8)]
+        else:
+            t = rng.choices(templates, weights)[0]
+            keep = list(t)
+            for j in rng.sample(range(8), rng.randrange(0, 7)):
+                keep[j] = (keep[j][0], "V", None)
+            args = [("x-match", "S", b"all")] + keep[: rng.randrange(1, 9)]
+        binds.append((q, rng.random() < 0.5, args))
+    msgs = []
+    for _ in range(n_msg):
+        t = list(rng.choices(templates, weights)[0])
+        if rng.random() < 0.3:
+            j = rng.randrange(8)
+            t[j] = (t[j][0],) + value(int(t[j][0][1:]))
+        rng.shuffle(t)
+        msgs.append(t)
+    return binds, msgs
+
+
+def _both(binds):
+    from chanamq_b200 import CHQ_HEADERS, CHQ_MODE_SPEC, GpuMatcher
+
+    m, o = GpuMatcher(CHQ_HEADERS, CHQ_MODE_SPEC), po.HeadersOracle()
+    for q, d, args in binds:
+        assert m.bind_args("", q, d, tbl(args)) == 0
+        assert o.bind(q, d, tbl(args)) == 0
+    return m, o
+
+
+def _same(m, o, tables, what=""):
+    blob, off = pack(tables)
+    got = m.route_headers_packed(blob, off)
+    w_off, w_ids, w_dur, w_err = o.route_packed(blob, off)
+    assert m.queue_names() == o.queue_names(), what
+    assert np.array_equal(got.err, w_err), what
+    if not np.array_equal(got.offsets, w_off):
+        i = max(int(np.nonzero(got.offsets != w_off)[0][0]) - 1, 0)
+        raise AssertionError("%s message %d: gpu %s oracle %s" % (what, i, got.queue_ids[got.offsets[i]:got.offsets[i + 1]],
+                                                                 w_ids[w_off[i]:w_off[i + 1]]))
+    assert np.array_equal(got.queue_ids, w_ids), what
+    assert np.array_equal(got.any_durable, w_dur), what
+    return got
+
+
+@pytest.mark.gpu
+def test_rule_examples_through_the_c_abi():
+    m, o = _both(BINDS)
+    got = _same(m, o, [tbl(x) for x, _ in MSGS] + [b"\x05abc", b"\x01a?", tbl([("a", "S", b"1")]) + b"\x09"])
+    names = m.queue_names()
+    for i, (_, want) in enumerate(MSGS):
+        assert {names[j].decode() for j in got.queue_ids[got.offsets[i]:got.offsets[i + 1]]} == want, i
+    assert got.err.tolist()[-3:] == [3, 3, 3]
+    assert m.bind_args("", "q", False, b"\x01a?") == -5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,n_bind,n_msg,n_queues,limits", [(1, 300, 4000, 300, (0, 0)), (2, 3000, 20000, 700, (0, 0)),
+                                                               (3, 3000, 8000, 50, (2, 4))])
+def test_config3_shape_against_the_oracle(seed, n_bind, n_msg, n_queues, limits):
+    binds, msgs = _workload(seed, n_bind, n_msg, n_queues)
+    m, o = _both(binds)
+    m.debug_limits(*limits)
+    got = _same(m, o, [tbl(x) for x in msgs], "seed %d" % seed)
+    mbar = len(got.queue_ids) / n_msg
+    assert mbar > 0.5, mbar
+
+
+@pytest.mark.gpu
+def test_headers_exchange_in_compat_mode_routes_by_key_like_the_reference():
+    """ExchangeEntity.scala:153,215: a headers exchange gets a TrieMatcher on the routing key"""
+    from chanamq_b200 import CHQ_HEADERS, CHQ_MODE_COMPAT, GpuMatcher
+
+    m, o = GpuMatcher(CHQ_HEADERS, CHQ_MODE_COMPAT), po.Oracle(po.HEADERS, po.COMPAT)
+    for k, q in [("a.*", "q1"), ("a.b", "q2"), ("#", "q3")]:
+        assert m.bind_args(k, q, False, tbl([("x-match", "S", b"any"), ("h", "S", b"v")])) == 0
+        o.bind(k, q)
+    blob, off = po.pack_keys(["a.b", "a.c", "#", "zzz"])
+    got = m.route_packed(blob, off)
+    w_off, w_ids, _, _ = o.route_packed(blob, off)
+    assert np.array_equal(got.offsets, w_off) and np.array_equal(got.queue_ids, w_ids)
