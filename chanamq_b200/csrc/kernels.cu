@@ -23,7 +23,7 @@
 #include "probe.cuh"
 
 #ifndef CHQ_MIN_CTAS
-#define CHQ_MIN_CTAS 6
+#define CHQ_MIN_CTAS 8
 #endif
 
 namespace chq {
@@ -74,10 +74,10 @@ constexpr uint64_t kFlagAgg = 1ull << 62, kFlagIncl = 2ull << 62, kValMask = (1u
 constexpr int kWarps = kRouteThreads / 32;
 
 struct RouteSmem {
-  uint32_t loff[kRouteSlots][kRouteThreads];  // per message: matched lists (offset, length), slot-major
+  // per message: matched lists (offset, length), slot-major.  While a key is being probed the same slots hold
+  // its unresolved tag hits (slot index, shape << 16 | literal mask): hit c is read before result c is written.
+  uint32_t loff[kRouteSlots][kRouteThreads];
   uint32_t llen[kRouteSlots][kRouteThreads];
-  uint32_t cslot[kRouteSlots][kRouteThreads];  // probe pass: tag hits still to be resolved (slot, shape)
-  uint32_t cshape[kRouteSlots][kRouteThreads]; // shape << 16 | literal mask
   uint64_t pos[kRouteThreads];                // final CSR position of the message's ids
   uint32_t cnt[kRouteThreads];
   uint16_t kcls[kRouteThreads];               // k | class << 8 | dedup << 12
@@ -291,20 +291,30 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
         uint32_t ncand = 0;
         probe_shapes(tv, kctx, e0, ne, tv.hashy_begin, nh, [&](uint32_t slot, uint32_t shape, uint32_t lit_mask) {
           if (ncand < (uint32_t)kRouteSlots) {
-            sm.cslot[ncand][tid] = slot;
-            sm.cshape[ncand][tid] = (shape << 16) | (lit_mask & 0xFFFFu);
+            sm.loff[ncand][tid] = slot;
+            sm.llen[ncand][tid] = (shape << 16) | (lit_mask & 0xFFFFu);
           }
           ++ncand;
         });
         overflow = ncand > (uint32_t)kRouteSlots;
-        for (uint32_t c = 0; c < min(ncand, (uint32_t)kRouteSlots); ++c)
-          resolve_candidate(tv, kctx, sm.cslot[c][tid], sm.cshape[c][tid] >> 16, sm.cshape[c][tid] & 0xFFFFu, record);
+        for (uint32_t c = 0; c < min(ncand, (uint32_t)kRouteSlots); ++c) {
+          const uint32_t slot = sm.loff[c][tid], sl = sm.llen[c][tid];
+          resolve_candidate(tv, kctx, slot, sl >> 16, sl & 0xFFFFu, [&](const GroupRec& rec) {
+            if (k > c) overflow = true;  // a chain gave more results than hits read so far: let the slow path redo it
+            else record(rec);
+          });
+        }
       }
     }
     // classify: 0 = count known, 1 = needs the de-duplicating merge to count, 2 = slow path
     int cls = 0;
     const bool dedup = (flags & kShared) != 0;
-    if (overflow) cls = 2;
+    // tiny: the whole result fits the 16-input sorting network of this thread (merge.cuh)
+    const bool tiny = !overflow && k >= 1 && k <= p.max_slots && ub <= (uint32_t)kTinyIds;
+    auto my_off = [&](uint32_t j) { return sm.loff[j][tid]; };
+    auto my_len = [&](uint32_t j) { return sm.llen[j][tid]; };
+    if (tiny) cnt = (k == 1 || !dedup) ? ub : tiny_union(tv.qlist, k, my_off, my_len, nullptr);
+    else if (overflow) cls = 2;
     else if (k <= 1) cnt = ub;
     else if (k > p.max_slots || ub - mxlen > p.max_small) cls = 2;
     else if (dedup) cls = 1;
@@ -356,11 +366,12 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
     if (lane == 31) sm.warp_sum[warp] = incl;
     // queue of routed messages for phase B (any order)
     {
-      const unsigned routed = __ballot_sync(kFull, cnt > 0);
+      const bool queued = cnt > 0 && !tiny;  // tiny messages are written by their own thread
+      const unsigned routed = __ballot_sync(kFull, queued);
       uint32_t qb = 0;
       if (lane == 0 && routed) qb = atomicAdd(&sm.q_n, (uint32_t)__popc(routed));
       qb = __shfl_sync(kFull, qb, 0);
-      if (cnt > 0) sm.queue[qb + __popc(routed & ((1u << lane) - 1))] = (uint16_t)tid;
+      if (queued) sm.queue[qb + __popc(routed & ((1u << lane) - 1))] = (uint16_t)tid;
     }
     sm.cnt[tid] = cnt;
     sm.kcls[tid] = (uint16_t)(min(k, 255u) | (cls << 8) | (dedup ? 1u << 12 : 0u));
@@ -415,7 +426,11 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RoutePara
     }
     __syncthreads();
 
-    // ---- phase B: warps pull routed messages off the tile's queue and write their unions ----
+    // ---- phase B: tiny messages by their own thread, the rest by warps off the tile's queue ----
+    if (tiny && cnt > 0 && !(p.debug & 1u)) {
+      const uint64_t o = sm.pos[tid];
+      if (o + cnt <= p.ids_cap) tiny_union(tv.qlist, k, my_off, my_len, p.ids + o);
+    }
     const uint32_t q_n = (p.debug & 1u) ? 0u : sm.q_n;
     for (;;) {
       uint32_t qi = 0;

@@ -5,11 +5,15 @@
 
 #include "chq_common.h"
 
+#ifndef CHQ_ROUTE_SMALL
+#define CHQ_ROUTE_SMALL 128
+#endif
+
 namespace chq {
 
 constexpr int kRouteThreads = 128;   // messages per tile; one thread per message while probing
 constexpr int kRouteSlots = 8;       // matched groups remembered per message before the slow path
-constexpr int kRouteSmall = 512;     // ids (all lists but the longest) a warp merges in shared memory
+constexpr int kRouteSmall = CHQ_ROUTE_SMALL;     // ids (all lists but the longest) a warp merges in shared memory
 
 // control words (device): zeroed before every launch
 constexpr int kCtrlTile = 0, kCtrlStatus = 1, kCtrlScratchLo = 2 /* u64 bump pointer */, kCtrlWords = 4;

@@ -82,6 +82,62 @@ __device__ __forceinline__ uint32_t lanes_below(uint32_t v, uint32_t x) {
   return q + (last < x ? 1u : 0u);
 }
 
+// ---- tiny messages: at most kTinyIds ids over ALL matched lists --------------------------------------
+// A third of the routed messages carry a handful of ids; giving each a whole warp costs hundreds of
+// instructions of set-up for a few stores.  Instead the message's own probing thread gathers the ids,
+// sorts them with a fixed 16-input bitonic network (static register indices, so all 32 lanes of the
+// warp run it in lock step whatever their data) and writes the distinct ones.
+constexpr int kTinyIds = 16;
+
+__device__ __forceinline__ void sort16(uint32_t (&v)[kTinyIds]) {
+#pragma unroll
+  for (int size = 2; size <= kTinyIds; size <<= 1) {
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+#pragma unroll
+      for (int i = 0; i < kTinyIds; ++i) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const bool up = (i & size) == 0;
+          const uint32_t a = v[i], b = v[j];
+          const uint32_t lo = min(a, b), hi = max(a, b);
+          v[i] = up ? lo : hi;
+          v[j] = up ? hi : lo;
+        }
+      }
+    }
+  }
+}
+
+// Gathers list j = qlist[off(j) .. off(j)+len(j)) for j < k (at most kTinyIds ids in total), sorts, and
+// returns the number of distinct ids; with out != null they are written to out[0 ...).
+template <typename Off, typename Len>
+__device__ __forceinline__ uint32_t tiny_union(const uint32_t* __restrict__ qlist, uint32_t k, Off off, Len len,
+                                               uint32_t* __restrict__ out) {
+  uint32_t tmp[kTinyIds];
+#pragma unroll
+  for (int s = 0; s < kTinyIds; ++s) tmp[s] = kNone;
+  uint32_t e = 0;
+  for (uint32_t j = 0; j < k; ++j) {
+    const uint32_t o = off(j), l = len(j);
+    for (uint32_t i = 0; i < l && e < (uint32_t)kTinyIds; ++i) tmp[e++] = __ldg(qlist + o + i);
+  }
+  uint32_t v[kTinyIds];
+#pragma unroll
+  for (int s = 0; s < kTinyIds; ++s) v[s] = tmp[s];
+  sort16(v);
+  uint32_t n = 0;
+#pragma unroll
+  for (int s = 0; s < kTinyIds; ++s) {
+    const bool keep = v[s] != kNone && (s == 0 || v[s] != v[s - 1]);
+    if (keep) {
+      if (out) out[n] = v[s];
+      ++n;
+    }
+  }
+  return n;
+}
+
 // Fast path of warp_union: the short lists hold at most 32 ids together (the usual case: one long
 // list plus a few one- or two-id lists).  The short ids live in one register per lane, are sorted
 // with shuffles, and are woven into the streamed long list one id at a time.
