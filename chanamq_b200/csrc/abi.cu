@@ -341,6 +341,13 @@ int32_t chq_table_create(chq_table** out, int32_t exchange_type, int32_t mode, i
   if (!t) return fail(CHQ_E_ARG, "out of host memory");
   t->device = device;
   t->host_only = device < 0;  // compiles and reports, but every route call fails: there is no CPU matcher
+  if (const char* s = getenv("CHQ_SCRATCH_IDS")) {  // test hook: a small slow-path arena, to exercise the grow-and-retry path
+    const size_t want = (size_t)strtoull(s, nullptr, 10);
+    if (want >= 64) {
+      for (auto& sl : t->slots) sl.ws.scratch_want = want;
+      t->dev_ws.scratch_want = want;
+    }
+  }
   if (!t->host_only) {
     cudaDeviceProp prop{};
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
@@ -521,7 +528,16 @@ int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
     // grow what was too small and run the batch again (inputs are still on the device)
     CU(cudaStreamSynchronize(s.st));
     if (status == CHQ_E_OVERFLOW) { if ((rc = s.d_ids.ensure(total + 1024))) return rc; }
-    else { s.ws.scratch_want = s.ws.scratch.cap * 4; s.ws.desc_want = std::max<size_t>(s.ws.desc_lists.cap, 1) * 4; }
+    else {
+      // the bump pointers kept counting past the end, so they say how much the batch really needs
+      const uint32_t n_tiles = (s.n + kRouteThreads - 1) / kRouteThreads;
+      uint64_t need_scratch = 0, need_desc = 0;
+      CU(cudaMemcpy(&need_scratch, s.ws.state.p + 1, sizeof(uint64_t), cudaMemcpyDeviceToHost));
+      CU(cudaMemcpy(&need_desc, s.ws.state.p + n_tiles + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost));
+      need_desc &= 0xFFFFFFFFull;
+      if (need_scratch > s.ws.scratch.cap) s.ws.scratch_want = (size_t)(need_scratch + need_scratch / 8 + 1024);
+      if (need_desc > s.ws.desc_lists.cap) s.ws.desc_want = (size_t)(need_desc + need_desc / 8 + 1024);
+    }
     if ((rc = slot_launch(t, s))) return rc;
   }
   const uint64_t total = s.r_total.p[0];

@@ -236,3 +236,21 @@ def test_device_entry_point_with_torch_buffers():
     assert (int(d_tot[1].item()) & 0xFFFFFFFF) == (-3 & 0xFFFFFFFF) and int(d_ids2[1000].item()) == -7
     fit = int(o_off[o_off <= 1000].max())  # messages that fit entirely are still written
     assert fit > 0 and np.array_equal(d_ids2[:fit].cpu().numpy().view(np.uint32), o_ids[:fit])
+
+
+@pytest.mark.parametrize("n", [1, 31, 32, 127, 128, 129, 255, 257, 1000])
+def test_batch_sizes_around_tile_edges(n):
+    w, m, o = _load_workload(2, 20_000, 5_000, CHQ_MODE_SPEC, True)
+    blob, off = w.keys(n, stream=100 + n)
+    r = assert_same_routing(m, o, blob, off)
+    check_csr_invariants(r, m.n_queues())
+
+
+def test_slow_path_arena_grows_and_retries(monkeypatch):
+    """host-level calls re-run a batch whose slow path ran out of scratch (CHQ_E_SCRATCH) with a larger arena"""
+    monkeypatch.setenv("CHQ_SCRATCH_IDS", "64")
+    w, m, o = _load_workload(2, 20_000, 2_000, CHQ_MODE_SPEC, True)
+    m.debug_limits(1, 1)  # every multi-list message takes the global-scratch path
+    blob, off = w.keys(40_000, stream=7)
+    r = assert_same_routing(m, o, blob, off, threads=4)
+    assert len(r.queue_ids) > 10_000
