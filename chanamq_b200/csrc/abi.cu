@@ -84,6 +84,8 @@ struct Workspace {
   DevBuf<uint8_t> nwords;
   DevBuf<uint64_t> state;   // [0..1] = control words, [2..] = per-tile scan state
   DevBuf<uint32_t> scratch;
+  DevBuf<uint32_t> cnt, meta;   // per message: id count, list count | class | flags (k_probe -> k_offsets, k_write)
+  DevBuf<uint2> mlist;          // per message: its lists (offset, length), kRouteSlots each
   DevBuf<uint32_t> desc_k;      // headers exchange: matched lists per message (k_headers_match -> k_route)
   DevBuf<uint32_t> desc_start;
   DevBuf<uint8_t> desc_flags;
@@ -95,7 +97,7 @@ struct Workspace {
   cudaEvent_t ev[kProfRing][3] = {};
   int prof_n = 0;
   void release() {
-    wid.release(); nwords.release(); state.release(); scratch.release();
+    wid.release(); nwords.release(); state.release(); scratch.release(); cnt.release(); meta.release(); mlist.release();
     desc_k.release(); desc_start.release(); desc_flags.release(); desc_lists.release();
     for (auto& e : ev) for (auto& x : e) if (x) { cudaEventDestroy(x); x = nullptr; }
     prof_n = 0;
@@ -229,7 +231,7 @@ int upload_table(chq_table* t) {
 int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint32_t* d_off, const uint32_t* d_klen, uint32_t n,
                   uint32_t* d_offsets, uint32_t* d_ids, uint64_t ids_cap, uint8_t* d_durable, uint8_t* d_err,
                   uint64_t* d_total, int32_t* d_status, cudaStream_t st) {
-  const uint32_t n_tiles = (n + kRouteThreads - 1) / kRouteThreads;
+  const uint32_t n_tiles = route_scan_tiles(n);
   const bool headers = t->ct.headers_mode;  // d_blob/d_off/d_klen then describe the messages' headers tables
   int rc;
   if (headers) {
@@ -241,9 +243,12 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
     if ((rc = ws.wid.ensure((size_t)n * t->tv.wstride + 4))) return rc;
     if ((rc = ws.nwords.ensure((size_t)n + 1))) return rc;
   }
-  if ((rc = ws.state.ensure((size_t)n_tiles + 3))) return rc;
+  if ((rc = ws.state.ensure((size_t)n_tiles + kStateHead))) return rc;
   if ((rc = ws.scratch.ensure(ws.scratch_want))) return rc;
-  CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + 3) * sizeof(uint64_t), st));
+  if ((rc = ws.cnt.ensure((size_t)n + 1))) return rc;
+  if ((rc = ws.meta.ensure((size_t)n + 1))) return rc;
+  if ((rc = ws.mlist.ensure((size_t)n * kRouteSlots + 1))) return rc;
+  CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + kStateHead) * sizeof(uint64_t), st));
   if (n == 0) {
     CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
     CU(cudaMemsetAsync(d_total, 0, sizeof(uint64_t), st));
@@ -261,7 +266,7 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   if (headers)
     CU(launch_headers_match(d_blob, d_off, d_klen, n, t->tv, ws.desc_k.p, ws.desc_start.p, ws.desc_flags.p, ws.desc_lists.p,
                             (uint32_t)std::min<size_t>(ws.desc_lists.cap, 0xFFFFFFFFu),
-                            reinterpret_cast<uint32_t*>(ws.state.p + n_tiles + 2), reinterpret_cast<uint32_t*>(ws.state.p) + kCtrlStatus,
+                            reinterpret_cast<uint32_t*>(ws.state.p) + kCtrlDescBump, reinterpret_cast<uint32_t*>(ws.state.p) + kCtrlStatus,
                             d_err, st));
   else if (d_klen) CU(launch_tokenize_keys(d_blob, d_off, d_klen, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
   else CU(launch_tokenize(d_blob, d_off, n, t->tv, split, ws.wid.p, ws.nwords.p, d_err, st));
@@ -278,7 +283,10 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   p.durable = d_durable;
   p.total = d_total;
   p.ctrl = reinterpret_cast<uint32_t*>(ws.state.p);
-  p.tile_state = ws.state.p + 2;
+  p.tile_state = ws.state.p + kStateHead;
+  p.cnt = ws.cnt.p;
+  p.meta = ws.meta.p;
+  p.mlist = ws.mlist.p;
   p.scratch = ws.scratch.p;
   p.scratch_cap = ws.scratch.cap;
   p.max_slots = t->max_slots;
@@ -530,11 +538,11 @@ int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
     if (status == CHQ_E_OVERFLOW) { if ((rc = s.d_ids.ensure(total + 1024))) return rc; }
     else {
       // the bump pointers kept counting past the end, so they say how much the batch really needs
-      const uint32_t n_tiles = (s.n + kRouteThreads - 1) / kRouteThreads;
       uint64_t need_scratch = 0, need_desc = 0;
+      uint32_t desc_used = 0;
       CU(cudaMemcpy(&need_scratch, s.ws.state.p + 1, sizeof(uint64_t), cudaMemcpyDeviceToHost));
-      CU(cudaMemcpy(&need_desc, s.ws.state.p + n_tiles + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost));
-      need_desc &= 0xFFFFFFFFull;
+      CU(cudaMemcpy(&desc_used, reinterpret_cast<uint32_t*>(s.ws.state.p) + kCtrlDescBump, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+      need_desc = desc_used;
       if (need_scratch > s.ws.scratch.cap) s.ws.scratch_want = (size_t)(need_scratch + need_scratch / 8 + 1024);
       if (need_desc > s.ws.desc_lists.cap) s.ws.desc_want = (size_t)(need_desc + need_desc / 8 + 1024);
     }
@@ -604,14 +612,17 @@ namespace {
 constexpr uint32_t kStaticMaxKeys = CHQ_STATIC_MAX_KEYS;     // keys per call
 constexpr uint32_t kStaticMaxWords = CHQ_STATIC_MAX_WORDS;   // keys x word-id stride of the table
 constexpr uint32_t kStaticArenaIds = 1u << 20;               // slow-path merge arena, in queue ids
-constexpr size_t kStaticTiles = (kStaticMaxKeys + kRouteThreads - 1) / kRouteThreads;
-constexpr size_t kStaticOffState = 0;                                                   // u64[2 + tiles]
-constexpr size_t kStaticOffNwords = ((2 + kStaticTiles) * 8 + 255) & ~size_t(255);      // u8[keys]
-constexpr size_t kStaticOffWid = (kStaticOffNwords + kStaticMaxKeys + 255) & ~size_t(255);  // u32[words]
-constexpr size_t kStaticOffArena = kStaticOffWid + (size_t)kStaticMaxWords * 4;         // u32[arena]
+constexpr size_t kStaticTiles = (kStaticMaxKeys + kRouteScanTile - 1) / kRouteScanTile;
+constexpr size_t kStaticOffState = 0;                                                            // u64[head + tiles]
+constexpr size_t kStaticOffNwords = ((kStateHead + kStaticTiles) * 8 + 255) & ~size_t(255);      // u8[keys]
+constexpr size_t kStaticOffCnt = (kStaticOffNwords + kStaticMaxKeys + 255) & ~size_t(255);       // u32[keys]
+constexpr size_t kStaticOffMeta = kStaticOffCnt + (size_t)kStaticMaxKeys * 4;                    // u32[keys]
+constexpr size_t kStaticOffMlist = kStaticOffMeta + (size_t)kStaticMaxKeys * 4;                  // uint2[keys][kRouteSlots]
+constexpr size_t kStaticOffWid = kStaticOffMlist + (size_t)kStaticMaxKeys * kRouteSlots * 8;     // u32[words]
+constexpr size_t kStaticOffArena = kStaticOffWid + (size_t)kStaticMaxWords * 4;                  // u32[arena]
 constexpr size_t kStaticBytes = kStaticOffArena + (size_t)kStaticArenaIds * 4;
 
-// About 6.3 MiB of device memory, held by every GPU that loads this library until the process exits.
+// About 11 MiB of device memory, held by every GPU that loads this library until the process exits.
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
 
 // In host code the name g_static_scratch is only a handle for the runtime, not a device address;
@@ -649,11 +660,11 @@ int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const 
   unsigned char* base = nullptr;
   if ((rc = static_scratch_ptr(t->device, &base))) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  const uint32_t n_tiles = (n + kRouteThreads - 1) / kRouteThreads;
+  const uint32_t n_tiles = route_scan_tiles(n);
   uint64_t* state = reinterpret_cast<uint64_t*>(base + kStaticOffState);
   // the array keeps whatever the previous call left: the control words and the per-tile scan state
   // must start at zero; the rows, counts and arena are fully rewritten before they are read
-  CU(cudaMemsetAsync(state, 0, ((size_t)n_tiles + 2) * sizeof(uint64_t), st));
+  CU(cudaMemsetAsync(state, 0, ((size_t)n_tiles + kStateHead) * sizeof(uint64_t), st));
   if (n == 0) {
     CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
     CU(cudaMemsetAsync(d_total, 0, sizeof(uint64_t), st));
@@ -676,7 +687,10 @@ int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const 
   p.durable = d_any_durable;
   p.total = d_total;
   p.ctrl = reinterpret_cast<uint32_t*>(state);
-  p.tile_state = state + 2;
+  p.tile_state = state + kStateHead;
+  p.cnt = reinterpret_cast<uint32_t*>(base + kStaticOffCnt);
+  p.meta = reinterpret_cast<uint32_t*>(base + kStaticOffMeta);
+  p.mlist = reinterpret_cast<uint2*>(base + kStaticOffMlist);
   p.scratch = reinterpret_cast<uint32_t*>(base + kStaticOffArena);
   p.scratch_cap = kStaticArenaIds;
   p.max_slots = t->max_slots;
@@ -707,11 +721,14 @@ int32_t chq_merge_slices_device(int32_t device, const uint32_t* d_slice_offsets,
   CU(cudaSetDevice(device));
   Workspace& ws = g_merge_ws[device];
   cudaStream_t st = (cudaStream_t)stream;
-  const uint32_t n_tiles = (n + kRouteThreads - 1) / kRouteThreads;
+  const uint32_t n_tiles = route_scan_tiles(n);
   int rc;
-  if ((rc = ws.state.ensure((size_t)n_tiles + 2))) return rc;
+  if ((rc = ws.state.ensure((size_t)n_tiles + kStateHead))) return rc;
   if ((rc = ws.scratch.ensure(ws.scratch_want))) return rc;
-  CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + 2) * sizeof(uint64_t), st));
+  if ((rc = ws.cnt.ensure((size_t)n + 1))) return rc;
+  if ((rc = ws.meta.ensure((size_t)n + 1))) return rc;
+  if ((rc = ws.mlist.ensure((size_t)n * kRouteSlots + 1))) return rc;
+  CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + kStateHead) * sizeof(uint64_t), st));
   if (n == 0) {
     CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
     CU(cudaMemsetAsync(d_total, 0, sizeof(uint64_t), st));
@@ -732,7 +749,10 @@ int32_t chq_merge_slices_device(int32_t device, const uint32_t* d_slice_offsets,
   p.durable = d_any_durable;
   p.total = d_total;
   p.ctrl = reinterpret_cast<uint32_t*>(ws.state.p);
-  p.tile_state = ws.state.p + 2;
+  p.tile_state = ws.state.p + kStateHead;
+  p.cnt = ws.cnt.p;
+  p.meta = ws.meta.p;
+  p.mlist = ws.mlist.p;
   p.scratch = ws.scratch.p;
   p.scratch_cap = ws.scratch.cap;
   p.max_slots = kRouteSlots;

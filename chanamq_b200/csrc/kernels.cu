@@ -3,15 +3,15 @@
 //   k_tokenize : routing-key bytes -> interned word ids        (replaces String.split + the per-level
 //                                                               String hashing of TrieMatcher.lookup,
 //                                                               QueueMatcher.scala:403-413, 261-263)
-//   k_route    : word ids x compiled table -> CSR of queue ids (replaces ilookup/bLookup,
+//   k_probe/k_offsets/k_write : word ids x compiled table -> CSR of queue ids (replaces ilookup/bLookup,
 //                                                               QueueMatcher.scala:523-585, and the
 //                                                               set/dedup/flag work of
 //                                                               ExchangeEntity.scala:297-302)
 //
-// k_route is ONE fused, persistent kernel per batch: probe -> exact per-message counts -> chained
-// (decoupled look-back) prefix sum across tiles -> merged, sorted, de-duplicated id lists written
-// straight to their final CSR position.  Inputs are read once and outputs written once; the table
-// (hash buckets, groups, queue lists) is L2-resident.  Integer/byte work throughout — no tensor
+// Routing a batch is k_tokenize, then three launches (k_probe -> k_offsets -> k_write): probe every
+// key against the compiled table and count its queues exactly, prefix-sum the counts into CSR
+// offsets, write the merged, sorted, de-duplicated id lists straight to their final position.
+// Inputs are read once and outputs written once; the table (tags, groups, queue lists) is L2-resident.  Integer/byte work throughout — no tensor
 // cores (there is no dense contraction on this path).
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -24,6 +24,9 @@
 
 #ifndef CHQ_MIN_CTAS
 #define CHQ_MIN_CTAS 8
+#endif
+#ifndef CHQ_WRITE_CTAS
+#define CHQ_WRITE_CTAS 8
 #endif
 
 namespace chq {
@@ -70,22 +73,14 @@ __global__ void __launch_bounds__(256) k_tokenize(const uint8_t* __restrict__ bl
 // ------------------------------------------------------------------------------------------
 namespace {
 
-constexpr uint64_t kFlagAgg = 1ull << 62, kFlagIncl = 2ull << 62, kValMask = (1ull << 62) - 1;
 constexpr int kWarps = kRouteThreads / 32;
 
-struct RouteSmem {
+struct RouteSmem {  // k_probe
   // per message: matched lists (offset, length), slot-major.  While a key is being probed the same slots hold
   // its unresolved tag hits (slot index, shape << 16 | literal mask): hit c is read before result c is written.
   uint32_t loff[kRouteSlots][kRouteThreads];
   uint32_t llen[kRouteSlots][kRouteThreads];
-  uint64_t pos[kRouteThreads];                // final CSR position of the message's ids
-  uint32_t cnt[kRouteThreads];
-  uint16_t kcls[kRouteThreads];               // k | class << 8 | dedup << 12
-  uint16_t queue[kRouteThreads];              // routed messages of this tile, any order
-  WarpScratch ws[kWarps];
-  uint64_t warp_sum[kWarps];
-  uint64_t tile_base;
-  uint32_t tile, q_n, q_next;
+  WarpScratch ws[kWarps];   // for counting unions that must de-duplicate
 };
 
 // Generic slow path for one message, by one warp: every matched list is appended to a piece of the
@@ -221,244 +216,281 @@ __device__ uint32_t warp_fallback_lists(const RouteParams& p, uint32_t my_off, u
 
 }  // namespace
 
-__global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_route(RouteParams p) {
+// ------------------------------------------------------------------------------------------
+// the route launch: three kernels on one stream
+//   k_probe   one thread per message: which queue lists apply, and how many ids the union has
+//   k_offsets exclusive prefix sum of the counts -> CSR offsets (single pass, chained look-back)
+//   k_write   one warp per routed message (tiny ones by a single thread): the sorted union, written once
+// No barrier separates a message's probing from anyone else's, and each kernel has its own
+// register budget; the per-message list descriptors (64 bytes) travel through global memory.
+// ------------------------------------------------------------------------------------------
+namespace {
+
+constexpr uint32_t kMetaTiny = 1u << 13, kMetaDedup = 1u << 12;  // meta = k | class << 8 | flags
+
+}  // namespace
+
+__global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RouteParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   RouteSmem& sm = *reinterpret_cast<RouteSmem*>(smem_raw);
   const TableView& tv = p.tv;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  volatile uint64_t* tstate = p.tile_state;
+  const uint32_t m = blockIdx.x * kRouteThreads + tid;
 
-  for (;;) {
-    __syncthreads();  // previous tile fully done with sm
-    if (tid == 0) {
-      sm.tile = atomicAdd(p.ctrl + kCtrlTile, 1u);
-      sm.q_n = 0;
-      sm.q_next = 0;
-    }
-    __syncthreads();
-    const uint32_t tile = sm.tile;
-    if (tile >= p.n_tiles) return;
-    const uint32_t m = tile * kRouteThreads + tid;
-
-    // ---- phase A: one thread per message: probe every compatible shape -------------------
-    uint32_t k = 0, ub = 0, mxlen = 0, flags = 0, cnt = 0, nw = 0;
-    const uint32_t* row = p.wid + (size_t)m * tv.wstride;
-    if (m < p.n && !p.slice_offsets && !p.desc_k) nw = p.nwords[m];
-    bool overflow = false;  // more tag hits than candidate slots: the slow path re-probes
-    if (p.slice_offsets || p.desc_k) nw = m < p.n ? 1u : 0u;
-    if (nw > 0 && !(p.debug & 2u)) {
-      auto record = [&](const GroupRec& rec) {
-        if (k < p.max_slots) { sm.loff[k][tid] = rec.list_off; sm.llen[k][tid] = rec.list_len; }
-        ++k;
-        ub += rec.list_len;
-        mxlen = max(mxlen, rec.list_len);
-        flags |= rec.flags;
-      };
-      if (p.slice_offsets) {  // merge of per-slice results: the lists are given, nothing to probe
-        for (uint32_t r = 0; r < p.n_slices; ++r) {
-          const uint32_t* so = p.slice_offsets + (size_t)r * (p.n + 1) + m;
-          const uint32_t a = __ldg(so), e = __ldg(so + 1);
-          if (e > a) {
-            GroupRec rec{};
-            rec.list_off = (uint32_t)(r * p.slice_cap + a);
-            rec.list_len = e - a;
-            rec.flags = kShared | (__ldg(p.slice_durable + (size_t)r * p.n + m) ? kAnyDurable : 0);
-            record(rec);
-          } else if (__ldg(p.slice_durable + (size_t)r * p.n + m)) {
-            flags |= kAnyDurable;
-          }
-        }
-      } else if (p.desc_k) {  // headers exchange: k_headers_match left the lists in global memory
-        const uint32_t kd = __ldg(p.desc_k + m);
-        const uint2* dl = p.desc_lists + __ldg(p.desc_start + m);
-        for (uint32_t j = 0; j < kd; ++j) {
-          const uint2 d = __ldg(dl + j);
+  uint32_t k = 0, ub = 0, mxlen = 0, flags = 0, cnt = 0, nw = 0;
+  const uint32_t* row = p.wid + (size_t)m * tv.wstride;
+  if (m < p.n && !p.slice_offsets && !p.desc_k) nw = p.nwords[m];
+  bool overflow = false;  // more tag hits than candidate slots: the slow path re-probes
+  if (p.slice_offsets || p.desc_k) nw = m < p.n ? 1u : 0u;
+  if (nw > 0 && !(p.debug & 2u)) {
+    auto record = [&](const GroupRec& rec) {
+      if (k < p.max_slots) { sm.loff[k][tid] = rec.list_off; sm.llen[k][tid] = rec.list_len; }
+      ++k;
+      ub += rec.list_len;
+      mxlen = max(mxlen, rec.list_len);
+      flags |= rec.flags;
+    };
+    if (p.slice_offsets) {  // merge of per-slice results: the lists are given, nothing to probe
+      for (uint32_t r = 0; r < p.n_slices; ++r) {
+        const uint32_t* so = p.slice_offsets + (size_t)r * (p.n + 1) + m;
+        const uint32_t a = __ldg(so), e = __ldg(so + 1);
+        if (e > a) {
           GroupRec rec{};
-          rec.list_off = d.x;
-          rec.list_len = d.y;
+          rec.list_off = (uint32_t)(r * p.slice_cap + a);
+          rec.list_len = e - a;
+          rec.flags = kShared | (__ldg(p.slice_durable + (size_t)r * p.n + m) ? kAnyDurable : 0);
           record(rec);
+        } else if (__ldg(p.slice_durable + (size_t)r * p.n + m)) {
+          flags |= kAnyDurable;
         }
-        flags |= __ldg(p.desc_flags + m);
-      } else if (tv.exchange_type == 1 /* fanout */) {
-        if (tv.fanout_group != kNone) record(load_group(tv, tv.fanout_group));
-      } else {
-        KeyCtx kctx;
-        key_ctx_init(kctx, row, nw, tv.wstride);
-        const uint32_t L = min(nw, (uint32_t)kLenCap);
-        const uint32_t e0 = nw <= (uint32_t)kLenCap ? tv.exact_rng[3 * L] : 0;
-        const uint32_t ne = nw <= (uint32_t)kLenCap ? tv.exact_rng[3 * L + 1] - e0 : 0;
-        const uint32_t nh = tv.exact_rng[3 * L + 2] - tv.hashy_begin;
-        uint32_t ncand = 0;
-        probe_shapes(tv, kctx, e0, ne, tv.hashy_begin, nh, [&](uint32_t slot, uint32_t shape, uint32_t lit_mask) {
-          if (ncand < (uint32_t)kRouteSlots) {
-            sm.loff[ncand][tid] = slot;
-            sm.llen[ncand][tid] = (shape << 16) | (lit_mask & 0xFFFFu);
-          }
-          ++ncand;
+      }
+    } else if (p.desc_k) {  // headers exchange: k_headers_match left the lists in global memory
+      const uint32_t kd = __ldg(p.desc_k + m);
+      const uint2* dl = p.desc_lists + __ldg(p.desc_start + m);
+      for (uint32_t j = 0; j < kd; ++j) {
+        const uint2 d = __ldg(dl + j);
+        GroupRec rec{};
+        rec.list_off = d.x;
+        rec.list_len = d.y;
+        record(rec);
+      }
+      flags |= __ldg(p.desc_flags + m);
+    } else if (tv.exchange_type == 1 /* fanout */) {
+      if (tv.fanout_group != kNone) record(load_group(tv, tv.fanout_group));
+    } else {
+      KeyCtx kctx;
+      key_ctx_init(kctx, row, nw, tv.wstride);
+      const uint32_t L = min(nw, (uint32_t)kLenCap);
+      const uint32_t e0 = nw <= (uint32_t)kLenCap ? tv.exact_rng[3 * L] : 0;
+      const uint32_t ne = nw <= (uint32_t)kLenCap ? tv.exact_rng[3 * L + 1] - e0 : 0;
+      const uint32_t nh = tv.exact_rng[3 * L + 2] - tv.hashy_begin;
+      uint32_t ncand = 0;
+      probe_shapes(tv, kctx, e0, ne, tv.hashy_begin, nh, [&](uint32_t slot, uint32_t shape, uint32_t lit_mask) {
+        if (ncand < (uint32_t)kRouteSlots) {
+          sm.loff[ncand][tid] = slot;
+          sm.llen[ncand][tid] = (shape << 16) | (lit_mask & 0xFFFFu);
+        }
+        ++ncand;
+      });
+      overflow = ncand > (uint32_t)kRouteSlots;
+      for (uint32_t c = 0; c < min(ncand, (uint32_t)kRouteSlots); ++c) {
+        const uint32_t slot = sm.loff[c][tid], sl = sm.llen[c][tid];
+        resolve_candidate(tv, kctx, slot, sl >> 16, sl & 0xFFFFu, [&](const GroupRec& rec) {
+          if (k > c) overflow = true;  // a chain gave more results than hits read so far: let the slow path redo it
+          else record(rec);
         });
-        overflow = ncand > (uint32_t)kRouteSlots;
-        for (uint32_t c = 0; c < min(ncand, (uint32_t)kRouteSlots); ++c) {
-          const uint32_t slot = sm.loff[c][tid], sl = sm.llen[c][tid];
-          resolve_candidate(tv, kctx, slot, sl >> 16, sl & 0xFFFFu, [&](const GroupRec& rec) {
-            if (k > c) overflow = true;  // a chain gave more results than hits read so far: let the slow path redo it
-            else record(rec);
-          });
-        }
       }
     }
-    // classify: 0 = count known, 1 = needs the de-duplicating merge to count, 2 = slow path
-    int cls = 0;
-    const bool dedup = (flags & kShared) != 0;
-    // tiny: the whole result fits the 16-input sorting network of this thread (merge.cuh)
-    const bool tiny = !overflow && k >= 1 && k <= p.max_slots && ub <= (uint32_t)kTinyIds;
-    auto my_off = [&](uint32_t j) { return sm.loff[j][tid]; };
-    auto my_len = [&](uint32_t j) { return sm.llen[j][tid]; };
-    if (tiny) cnt = (k == 1 || !dedup) ? ub : tiny_union(tv.qlist, k, my_off, my_len, nullptr);
-    else if (overflow) cls = 2;
-    else if (k <= 1) cnt = ub;
-    else if (k > p.max_slots || ub - mxlen > p.max_small) cls = 2;
-    else if (dedup) cls = 1;
-    else cnt = ub;
+  }
+  // classify: 0 = count known, 1 = needs the de-duplicating merge to count, 2 = slow path (result parked in scratch)
+  int cls = 0;
+  const bool dedup = (flags & kShared) != 0;
+  // tiny: the whole result fits the 16-input sorting network of one thread (merge.cuh)
+  const bool tiny = !overflow && k >= 1 && k <= p.max_slots && ub <= (uint32_t)kTinyIds;
+  auto my_off = [&](uint32_t j) { return sm.loff[j][tid]; };
+  auto my_len = [&](uint32_t j) { return sm.llen[j][tid]; };
+  if (tiny) cnt = (k == 1 || !dedup) ? ub : tiny_union(tv.qlist, k, my_off, my_len, nullptr);
+  else if (overflow) cls = 2;
+  else if (k <= 1) cnt = ub;
+  else if (k > p.max_slots || ub - mxlen > p.max_small) cls = 2;
+  else if (dedup) cls = 1;
+  else cnt = ub;
 
-    __syncwarp();
-    for (unsigned todo = __ballot_sync(kFull, cls == 2); todo; todo &= todo - 1) {
-      const int src = __ffs(todo) - 1;
-      const uint32_t mm = tile * kRouteThreads + warp * 32 + src;
-      uint64_t so;
-      uint32_t fl;
-      uint32_t c;
-      if (p.desc_k) {  // more lists than shared-memory slots: read the descriptors again
-        fl = __shfl_sync(kFull, flags, src);
-        c = warp_fallback_desc(p, p.desc_lists + __ldg(p.desc_start + mm), __shfl_sync(kFull, k, src), lane, &so);
-      } else if (p.slice_offsets) {  // lists are in shared memory (at most n_slices <= kRouteSlots of them)
-        const int kk = __shfl_sync(kFull, k, src);
-        uint32_t o = 0, l = 0;
-        if (lane < kk) { o = sm.loff[lane][warp * 32 + src]; l = sm.llen[lane][warp * 32 + src]; }
-        fl = __shfl_sync(kFull, flags, src);
-        c = warp_fallback_lists(p, o, l, kk, lane, &so);
-      } else {
-        c = warp_fallback(p, p.wid + (size_t)mm * tv.wstride, __shfl_sync(kFull, nw, src), lane, &so, &fl);
-      }
-      if (lane == src) {
-        cnt = c;
-        flags = fl;
-        sm.loff[0][tid] = (uint32_t)so;
-        sm.llen[0][tid] = (uint32_t)(so >> 32);
-      }
-    }
-    for (unsigned todo = __ballot_sync(kFull, cls == 1); todo; todo &= todo - 1) {
-      const int src = __ffs(todo) - 1;
+  uint64_t scr = 0;
+  __syncwarp();
+  for (unsigned todo = __ballot_sync(kFull, cls == 2); todo; todo &= todo - 1) {
+    const int src = __ffs(todo) - 1;
+    const uint32_t mm = blockIdx.x * kRouteThreads + warp * 32 + src;
+    uint64_t so;
+    uint32_t fl;
+    uint32_t c;
+    if (p.desc_k) {  // more lists than slots: read the descriptors again
+      fl = __shfl_sync(kFull, flags, src);
+      c = warp_fallback_desc(p, p.desc_lists + __ldg(p.desc_start + mm), __shfl_sync(kFull, k, src), lane, &so);
+    } else if (p.slice_offsets) {  // lists are in shared memory (at most n_slices <= kRouteSlots of them)
       const int kk = __shfl_sync(kFull, k, src);
       uint32_t o = 0, l = 0;
       if (lane < kk) { o = sm.loff[lane][warp * 32 + src]; l = sm.llen[lane][warp * 32 + src]; }
-      const uint32_t c = warp_union<false>(tv.qlist, o, l, kk, true, sm.ws[warp], nullptr, 0, 0, lane);
-      if (lane == src) cnt = c;
+      fl = __shfl_sync(kFull, flags, src);
+      c = warp_fallback_lists(p, o, l, kk, lane, &so);
+    } else {
+      c = warp_fallback(p, p.wid + (size_t)mm * tv.wstride, __shfl_sync(kFull, nw, src), lane, &so, &fl);
     }
-    if (m < p.n) p.durable[m] = (flags & kAnyDurable) ? 1 : 0;
+    if (lane == src) { cnt = c; flags = fl; scr = so; }
+  }
+  for (unsigned todo = __ballot_sync(kFull, cls == 1); todo; todo &= todo - 1) {
+    const int src = __ffs(todo) - 1;
+    const int kk = __shfl_sync(kFull, k, src);
+    uint32_t o = 0, l = 0;
+    if (lane < kk) { o = sm.loff[lane][warp * 32 + src]; l = sm.llen[lane][warp * 32 + src]; }
+    const uint32_t c = warp_union<false>(tv.qlist, o, l, kk, true, sm.ws[warp], nullptr, 0, 0, lane);
+    if (lane == src) cnt = c;
+  }
+  if (m >= p.n) return;
+  p.durable[m] = (flags & kAnyDurable) ? 1 : 0;
+  p.cnt[m] = cnt;
+  p.meta[m] = min(k, 255u) | ((uint32_t)cls << 8) | (dedup ? kMetaDedup : 0u) | (tiny ? kMetaTiny : 0u);
+  uint2* lists = p.mlist + (size_t)m * kRouteSlots;
+  if (cls == 2) {
+    lists[0] = make_uint2((uint32_t)scr, (uint32_t)(scr >> 32));
+  } else if (cnt > 0) {
+    for (uint32_t j = 0; j < k; ++j) lists[j] = make_uint2(sm.loff[j][tid], sm.llen[j][tid]);
+  }
+}
 
-    // ---- tile prefix sum + chained scan across tiles ---------------------------------------
-    uint64_t incl = cnt;
+// Exclusive prefix sum of cnt[0..n) -> offsets[0..n], one pass: tiles of kScanTile counts, each tile adds up
+// its own, publishes the aggregate and looks back over its predecessors' (tiles finish fast, so the look-back
+// is short).  The last tile writes offsets[n], the total and the overflow status.
+constexpr int kScanThreads = 256, kScanPer = 4, kScanTile = kScanThreads * kScanPer;
+constexpr uint64_t kFlagAgg = 1ull << 62, kFlagIncl = 2ull << 62, kValMask = (1ull << 62) - 1;
+static_assert(kScanTile == kRouteScanTile, "abi.cu sizes the tile state with kRouteScanTile");
+
+__global__ void __launch_bounds__(kScanThreads) k_offsets(RouteParams p) {
+  __shared__ uint64_t warp_sum[kScanThreads / 32];
+  __shared__ uint64_t tile_base;
+  __shared__ uint32_t tile_id;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  volatile uint64_t* tstate = p.tile_state;
+  if (tid == 0) tile_id = atomicAdd(p.ctrl + kCtrlTile, 1u);  // tiles in launch order: predecessors always run
+  __syncthreads();
+  const uint32_t tile = tile_id;
+  const uint32_t base = tile * kScanTile + tid * kScanPer;
+  uint32_t v[kScanPer];
+  uint64_t mine = 0;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint64_t v = __shfl_up_sync(kFull, incl, d);
-      if (lane >= d) incl += v;
-    }
-    if (lane == 31) sm.warp_sum[warp] = incl;
-    // queue of routed messages for phase B (any order)
-    {
-      const bool queued = cnt > 0 && !tiny;  // tiny messages are written by their own thread
-      const unsigned routed = __ballot_sync(kFull, queued);
-      uint32_t qb = 0;
-      if (lane == 0 && routed) qb = atomicAdd(&sm.q_n, (uint32_t)__popc(routed));
-      qb = __shfl_sync(kFull, qb, 0);
-      if (queued) sm.queue[qb + __popc(routed & ((1u << lane) - 1))] = (uint16_t)tid;
-    }
-    sm.cnt[tid] = cnt;
-    sm.kcls[tid] = (uint16_t)(min(k, 255u) | (cls << 8) | (dedup ? 1u << 12 : 0u));
-    __syncthreads();
-    uint64_t warp_base = 0, tile_total = 0;
+  for (int i = 0; i < kScanPer; ++i) {
+    v[i] = base + i < p.n ? p.cnt[base + i] : 0;
+    mine += v[i];
+  }
+  uint64_t incl = mine;
 #pragma unroll
-    for (int w = 0; w < kWarps; ++w) {
-      const uint64_t v = sm.warp_sum[w];
-      if (w < warp) warp_base += v;
-      tile_total += v;
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint64_t t = __shfl_up_sync(kFull, incl, d);
+    if (lane >= d) incl += t;
+  }
+  if (lane == 31) warp_sum[warp] = incl;
+  __syncthreads();
+  uint64_t warp_base = 0, tile_total = 0;
+#pragma unroll
+  for (int w = 0; w < kScanThreads / 32; ++w) {
+    const uint64_t s = warp_sum[w];
+    if (w < warp) warp_base += s;
+    tile_total += s;
+  }
+  if (warp == 0) {
+    if (lane == 0) {
+      tstate[tile] = (tile == 0 ? kFlagIncl : kFlagAgg) | tile_total;
+      __threadfence();
     }
-    if (warp == 0) {
-      if (lane == 0) {
-        tstate[tile] = (tile == 0 ? kFlagIncl : kFlagAgg) | tile_total;
+    uint64_t excl = 0;
+    for (int64_t j = (int64_t)tile - 1; j >= 0; j -= 32) {
+      const int64_t idx = j - lane;
+      uint64_t s;
+      do {
+        s = kFlagIncl;
+        if (idx >= 0) s = tstate[idx];
+      } while (__any_sync(kFull, (s >> 62) == 0));
+      const unsigned im = __ballot_sync(kFull, (s >> 62) == 2);
+      const int stop = im ? __ffs(im) - 1 : 31;
+      uint64_t c = lane <= stop ? (s & kValMask) : 0;
+#pragma unroll
+      for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(kFull, c, d);
+      excl += c;
+      if (im) break;
+    }
+    if (lane == 0) {
+      if (tile > 0) {
+        tstate[tile] = kFlagIncl | (excl + tile_total);
         __threadfence();
       }
-      uint64_t excl = 0;
-      for (int64_t j = (int64_t)tile - 1; j >= 0; j -= 32) {
-        const int64_t idx = j - lane;
-        uint64_t v;
-        do {
-          v = kFlagIncl;
-          if (idx >= 0) v = tstate[idx];
-        } while (__any_sync(kFull, (v >> 62) == 0));
-        const unsigned im = __ballot_sync(kFull, (v >> 62) == 2);
-        const int stop = im ? __ffs(im) - 1 : 31;
-        uint64_t c = lane <= stop ? (v & kValMask) : 0;
+      tile_base = excl;
+      if (tile == p.n_tiles - 1) {
+        const uint64_t total = excl + tile_total;
+        *p.total = total;
+        p.offsets[p.n] = (uint32_t)min(total, (uint64_t)0xFFFFFFFFull);
+        if (total > 0xFFFFFFFFull || total > p.ids_cap) atomicOr(p.ctrl + kCtrlStatus, kStatusOverflow);
+      }
+    }
+  }
+  __syncthreads();
+  uint64_t pos = tile_base + warp_base + (incl - mine);
 #pragma unroll
-        for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(kFull, c, d);
-        excl += c;
-        if (im) break;
-      }
-      if (lane == 0) {
-        if (tile > 0) {
-          tstate[tile] = kFlagIncl | (excl + tile_total);
-          __threadfence();
-        }
-        sm.tile_base = excl;
-        if (tile == p.n_tiles - 1) {
-          const uint64_t total = excl + tile_total;
-          *p.total = total;
-          p.offsets[p.n] = (uint32_t)min(total, (uint64_t)0xFFFFFFFFull);
-          if (total > 0xFFFFFFFFull || total > p.ids_cap) atomicOr(p.ctrl + kCtrlStatus, kStatusOverflow);
-        }
-      }
-    }
-    __syncthreads();
-    {
-      const uint64_t pos = sm.tile_base + warp_base + (incl - cnt);
-      sm.pos[tid] = pos;
-      if (m < p.n) p.offsets[m] = (uint32_t)min(pos, (uint64_t)0xFFFFFFFFull);
-    }
-    __syncthreads();
+  for (int i = 0; i < kScanPer; ++i) {
+    if (base + i < p.n) p.offsets[base + i] = (uint32_t)min(pos, (uint64_t)0xFFFFFFFFull);
+    pos += v[i];
+  }
+}
 
-    // ---- phase B: tiny messages by their own thread, the rest by warps off the tile's queue ----
-    if (tiny && cnt > 0 && !(p.debug & 1u)) {
-      const uint64_t o = sm.pos[tid];
-      if (o + cnt <= p.ids_cap) tiny_union(tv.qlist, k, my_off, my_len, p.ids + o);
+__global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RouteParams p) {
+  __shared__ WarpScratch ws_all[kRouteThreads / 32];
+  const TableView& tv = p.tv;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  WarpScratch& ws = ws_all[warp];
+  const uint32_t n_chunks = (p.n + 31) / 32;
+  if (*p.total > 0xFFFFFFFFull || (p.debug & 1u)) return;  // offsets saturated: the launch reports CHQ_E_OVERFLOW
+  for (;;) {
+    uint32_t chunk = 0;
+    if (lane == 0) chunk = atomicAdd(p.ctrl + kCtrlChunk, 1u);  // 32 consecutive messages per grab
+    chunk = __shfl_sync(kFull, chunk, 0);
+    if (chunk >= n_chunks) return;
+    const uint32_t m = chunk * 32 + lane;
+    uint32_t cnt = 0, meta = 0, pos = 0;
+    if (m < p.n) {
+      cnt = p.cnt[m];
+      meta = p.meta[m];
+      pos = p.offsets[m];
     }
-    const uint32_t q_n = (p.debug & 1u) ? 0u : sm.q_n;
-    for (;;) {
-      uint32_t qi = 0;
-      if (lane == 0) qi = atomicAdd(&sm.q_next, 1u);
-      qi = __shfl_sync(kFull, qi, 0);
-      if (qi >= q_n) break;
-      const int t = sm.queue[qi];
-      const uint32_t c = sm.cnt[t];
-      const uint32_t kc = sm.kcls[t];
-      const int kk = kc & 0xFF, cl = (kc >> 8) & 0xF;
-      const uint64_t o = sm.pos[t];
-      if (o + c > p.ids_cap) continue;  // does not fit: the launch reports CHQ_E_OVERFLOW; nothing is written past ids_cap
+    const bool fits = (uint64_t)pos + cnt <= p.ids_cap;  // else CHQ_E_OVERFLOW: nothing is written past ids_cap
+    const uint2* lists = p.mlist + (size_t)m * kRouteSlots;
+    if ((meta & kMetaTiny) && cnt > 0 && fits) {  // tiny messages: their own lane gathers, sorts and writes
+      auto off = [&](uint32_t j) { return __ldg(lists + j).x; };
+      auto len = [&](uint32_t j) { return __ldg(lists + j).y; };
+      tiny_union(tv.qlist, meta & 0xFF, off, len, p.ids + pos);
+    }
+    __syncwarp();
+    for (unsigned todo = __ballot_sync(kFull, cnt > 0 && fits && !(meta & kMetaTiny)); todo; todo &= todo - 1) {
+      const int src = __ffs(todo) - 1;
+      const uint32_t c = __shfl_sync(kFull, cnt, src), mt = __shfl_sync(kFull, meta, src);
+      const uint64_t o = __shfl_sync(kFull, pos, src);
+      const int kk = mt & 0xFF, cl = (mt >> 8) & 0xF;
+      const uint2* ml = p.mlist + (size_t)(chunk * 32 + src) * kRouteSlots;
       if (cl == 2) {
-        const uint64_t so = ((uint64_t)sm.llen[0][t] << 32) | sm.loff[0][t];
+        const uint2 s2 = __ldg(ml);
+        const uint64_t so = ((uint64_t)s2.y << 32) | s2.x;
         for (uint32_t i = lane; i < c; i += 32) p.ids[o + i] = p.scratch[so + i];
       } else if (kk == 1) {
-        const uint32_t* src = tv.qlist + sm.loff[0][t] + lane;
+        const uint32_t* sp = tv.qlist + __ldg(ml).x + lane;
         uint32_t* dst = p.ids + o + lane;
         uint32_t i = lane;
-        for (; i + 96 < c; i += 128, src += 128, dst += 128) {
-          const uint32_t v0 = __ldg(src), v1 = __ldg(src + 32), v2 = __ldg(src + 64), v3 = __ldg(src + 96);
+        for (; i + 96 < c; i += 128, sp += 128, dst += 128) {
+          const uint32_t v0 = __ldg(sp), v1 = __ldg(sp + 32), v2 = __ldg(sp + 64), v3 = __ldg(sp + 96);
           dst[0] = v0; dst[32] = v1; dst[64] = v2; dst[96] = v3;
         }
-        for (; i < c; i += 32, src += 32, dst += 32) *dst = __ldg(src);
+        for (; i < c; i += 32, sp += 32, dst += 32) *dst = __ldg(sp);
       } else {
         uint32_t lo = 0, ll = 0;
-        if (lane < kk) { lo = sm.loff[lane][t]; ll = sm.llen[lane][t]; }
-        warp_union<true>(tv.qlist, lo, ll, kk, (kc >> 12) & 1, sm.ws[warp], p.ids, o, p.ids_cap, lane);
+        if (lane < kk) { const uint2 d = __ldg(ml + lane); lo = d.x; ll = d.y; }
+        warp_union<true>(tv.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, p.ids_cap, lane);
       }
     }
   }
@@ -487,6 +519,7 @@ cudaError_t launch_tokenize_keys(const uint8_t* bytes, const uint32_t* key_off, 
   return cudaGetLastError();
 }
 
+
 __global__ void k_finish(const uint32_t* ctrl, int32_t* status) {
   const uint32_t s = ctrl[kCtrlStatus];
   *status = (s & kStatusScratch) ? CHQ_E_SCRATCH : (s & kStatusOverflow) ? CHQ_E_OVERFLOW : CHQ_OK;
@@ -499,24 +532,22 @@ cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t 
 }
 
 cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st) {
-  if (p.n_tiles == 0) return cudaSuccess;
+  if (p.n == 0) return cudaSuccess;
   static int occ_by_dev[64] = {};
-  const int smem = (int)sizeof(RouteSmem);
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   int& occ = occ_by_dev[dev & 63];
-  if (occ == 0) {  // once per device: opt in to the shared-memory size, size the persistent grid
-    e = cudaFuncSetAttribute(k_route, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_route, kRouteThreads, smem);
+  if (occ == 0) {  // once per device: size the persistent grid of the write kernel
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_write, kRouteThreads, 0);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
   }
-  const uint64_t want = (uint64_t)n_sms * occ;
-  const uint32_t grid = (uint32_t)(p.n_tiles < want ? p.n_tiles : want);
-  k_route<<<grid, kRouteThreads, smem, st>>>(p);
-  ++g_launches;
+  k_probe<<<(p.n + kRouteThreads - 1) / kRouteThreads, kRouteThreads, sizeof(RouteSmem), st>>>(p);
+  k_offsets<<<p.n_tiles, kScanThreads, 0, st>>>(p);
+  const uint64_t want = (uint64_t)n_sms * occ, chunks = (p.n + 31) / 32;
+  k_write<<<(uint32_t)(chunks < want ? chunks : want), kRouteThreads, 0, st>>>(p);
+  g_launches += 3;
   return cudaGetLastError();
 }
 

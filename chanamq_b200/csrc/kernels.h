@@ -16,8 +16,11 @@ constexpr int kRouteSlots = 8;       // matched groups remembered per message be
 constexpr int kRouteSmall = CHQ_ROUTE_SMALL;     // ids (all lists but the longest) a warp merges in shared memory
 
 // control words (device): zeroed before every launch
-constexpr int kCtrlTile = 0, kCtrlStatus = 1, kCtrlScratchLo = 2 /* u64 bump pointer */, kCtrlWords = 4;
-// the headers matcher keeps its descriptor-arena bump pointer in the word after the tile state
+constexpr int kCtrlTile = 0 /* scan tile counter */, kCtrlStatus = 1, kCtrlScratchLo = 2 /* u64 bump pointer */,
+              kCtrlChunk = 4 /* write-kernel work counter */, kCtrlDescBump = 5 /* headers descriptor arena */, kCtrlWords = 8;
+constexpr int kRouteScanTile = 1024;  // counts per tile of the offsets scan
+constexpr int kStateHead = kCtrlWords / 2;  // the control words take the first kStateHead u64 of the state array
+inline uint32_t route_scan_tiles(uint32_t n) { return (n + kRouteScanTile - 1) / kRouteScanTile; }
 
 constexpr uint32_t kStatusOverflow = 1, kStatusScratch = 2;
 
@@ -31,7 +34,10 @@ struct RouteParams {
   uint64_t ids_cap;
   uint8_t* durable;          // [n] out
   uint64_t* total;           // out: number of ids
-  uint64_t* tile_state;      // [n_tiles] scratch, zeroed before launch
+  uint32_t* cnt;             // [n] scratch: ids per message (k_probe -> k_offsets, k_write)
+  uint32_t* meta;            // [n] scratch: lists | class << 8 | flags
+  uint2* mlist;              // [n][kRouteSlots] scratch: the message's lists (offset, length)
+  uint64_t* tile_state;      // [n_tiles] scratch of the offsets scan, zeroed before launch
   uint32_t* ctrl;            // [kCtrlWords] scratch, zeroed before launch
   uint32_t* scratch;         // slow-path arena
   uint64_t scratch_cap;      // in ids
