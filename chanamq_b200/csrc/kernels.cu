@@ -26,7 +26,7 @@
 #define CHQ_MIN_CTAS 8
 #endif
 #ifndef CHQ_WRITE_CTAS
-#define CHQ_WRITE_CTAS 8
+#define CHQ_WRITE_CTAS 10
 #endif
 
 namespace chq {
