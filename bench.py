@@ -240,7 +240,8 @@ def run_ours(a, rank, world, local_rank):
     barrier()
     dev_ms = e0.elapsed_time(e1)
     launches = L.chq_kernel_launches() - launches0
-    tok_ms, route_ms, prof_n = m.profile(False)
+    kms, prof_n = m.profile_kernels(False)
+    tok_ms, route_ms = kms["k_tokenize"], kms["k_probe"] + kms["k_offsets"] + kms["k_write"]
     tot = d_tot.cpu().numpy().reshape(N_BATCHES, 2)
     used = sorted({(a.warmup + i) % N_BATCHES for i in range(a.steps)} | {i % N_BATCHES for i in range(a.warmup)})
     if any((int(tot[b, 1]) & 0xFFFFFFFF) != 0 for b in used):
@@ -293,9 +294,11 @@ def run_ours(a, rank, world, local_rank):
         except Exception:
             pass
         wp = st["pattern_words"] / max(1, st["bindings"])
-        # B_topic = N(4 W + 4 + 4 M + 4) + P(4 Wp + 8), per k_route launch
+        # B_topic = N(4 W + 4 + 4 M + 4) + P(4 Wp + 8), per batch, charged to the three route kernels
+        # (k_probe + k_offsets + k_write: one launch group per batch); k_write alone moves N(4 M + 4 + 1) + 4 P of it
         alg_bytes = n * (4 * wbar + 4 + 4 * mbar + 4) + st["bindings"] * (4 * wp + 8)
         route_ms_avg = route_ms / max(1, prof_n)
+        write_bytes = n * (4 * mbar + 4 + 1) + 4 * st["bindings"]
         achieved = alg_bytes / (route_ms_avg * 1e-3) / 1e9
         traffic = None
         try:
@@ -317,7 +320,13 @@ def run_ours(a, rank, world, local_rank):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks, "unit": "GB/s", "frac": achieved / peaks,
-                         "traffic": traffic, "kernel": "k_route", "kernel_ms": route_ms_avg,
+                         "traffic": traffic, "kernel": "route group = k_probe + k_offsets + k_write (one each per batch)",
+                         "kernel_ms": route_ms_avg,
+                         "per_kernel_ms": {k: v / max(1, prof_n) for k, v in kms.items()},
+                         "dominant": {"kernel": "k_write", "ms": kms["k_write"] / max(1, prof_n),
+                                      "algorithmic_bytes_per_launch": write_bytes,
+                                      "achieved": write_bytes / (kms["k_write"] / max(1, prof_n) * 1e-3) / 1e9,
+                                      "frac": write_bytes / (kms["k_write"] / max(1, prof_n) * 1e-3) / 1e9 / peaks},
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                          "tokenize_ms": tok_ms / max(1, prof_n), "kernel_share_of_step": route_ms / dev_ms if world == 1 else None},
         }

@@ -71,6 +71,7 @@ def load_library():
         "chq_host_free": (i32, [vp]),
         "chq_stats": (i32, [vp, C.c_char_p, u32]),
         "chq_profile": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(u32)]),
+        "chq_profile_kernels": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(u32)]),
         "chq_kernel_launches": (u64, []),
         "chq_debug_limits": (i32, [vp, u32, u32]),
     }

@@ -94,7 +94,7 @@ struct Workspace {
   size_t desc_want = 1u << 20;  // descriptor arena (grown after CHQ_E_SCRATCH)
   // optional per-kernel timing (chq_profile): events on the launching stream around each kernel
   static constexpr int kProfRing = 256;
-  cudaEvent_t ev[kProfRing][3] = {};
+  cudaEvent_t ev[kProfRing][5] = {};  // start, after tokenize, after k_probe, after k_offsets, after k_write
   int prof_n = 0;
   void release() {
     wid.release(); nwords.release(); state.release(); scratch.release(); cnt.release(); meta.release(); mlist.release();
@@ -141,6 +141,8 @@ struct chq_table {
   // device copy of the compiled table
   DevBuf<DictSlot> d_dict;
   DevBuf<uint8_t> d_dict_bytes;
+  DevBuf<WordSlot> d_wdict;
+  DevBuf<uint32_t> d_wdict_off;
   DevBuf<Shape> d_shapes;
   DevBuf<uint16_t> d_exact;
   DevBuf<uint16_t> d_tags;
@@ -175,6 +177,8 @@ int upload_table(chq_table* t) {
   int rc;
   if ((rc = t->d_dict.upload(c.dict.data(), c.dict.size(), st))) return rc;
   if ((rc = t->d_dict_bytes.upload(c.dict_bytes.data(), c.dict_bytes.size(), st))) return rc;
+  if ((rc = t->d_wdict.upload(c.wdict.data(), c.wdict.size(), st))) return rc;
+  if ((rc = t->d_wdict_off.upload(c.wdict_off.data(), c.wdict_off.size(), st))) return rc;
   if ((rc = t->d_shapes.upload(c.shapes.data(), c.shapes.size(), st))) return rc;
   if ((rc = t->d_exact.upload(c.exact_rng.data(), c.exact_rng.size(), st))) return rc;
   if ((rc = t->d_tags.upload(c.tags.data(), c.tags.size(), st))) return rc;
@@ -209,6 +213,9 @@ int upload_table(chq_table* t) {
   v.dict = t->d_dict.p;
   v.dict_bytes = t->d_dict_bytes.p;
   v.dict_mask = (uint32_t)c.dict.size() - 1;
+  v.wdict = t->d_wdict.p;
+  v.wdict_off = t->d_wdict_off.p;
+  v.wdict_mask = (uint32_t)c.wdict.size() - 1;
   v.shapes = t->d_shapes.p;
   v.exact_rng = t->d_exact.p;
   v.hashy_begin = c.hashy_begin;
@@ -259,7 +266,7 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   cudaEvent_t* pe = nullptr;
   if (t->profile && ws.prof_n < Workspace::kProfRing) {
     pe = ws.ev[ws.prof_n++];
-    for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 5; ++i)
       if (!pe[i]) CU(cudaEventCreate(&pe[i]));
     CU(cudaEventRecord(pe[0], st));
   }
@@ -293,8 +300,8 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   p.max_small = t->max_small;
   if (headers) { p.desc_k = ws.desc_k.p; p.desc_start = ws.desc_start.p; p.desc_flags = ws.desc_flags.p; p.desc_lists = ws.desc_lists.p; }
   { const char* dbg = getenv("CHQ_DEBUG"); p.debug = dbg ? (uint32_t)atoi(dbg) : 0u; }
-  CU(launch_route(p, t->n_sms, st));
-  if (pe) CU(cudaEventRecord(pe[2], st));
+  CU(launch_route(p, t->n_sms, st, pe ? pe + 2 : nullptr));
+  if (pe) CU(cudaEventRecord(pe[4], st));
   CU(launch_finish(p.ctrl, d_status, st));
   t->n_batches++;
   t->n_messages += n;
@@ -375,7 +382,7 @@ int32_t chq_table_destroy(chq_table* t) {
   cudaDeviceSynchronize();
   for (auto& s : t->slots) s.release();
   t->dev_ws.release();
-  t->d_dict.release(); t->d_dict_bytes.release(); t->d_shapes.release(); t->d_exact.release();
+  t->d_dict.release(); t->d_dict_bytes.release(); t->d_wdict.release(); t->d_wdict_off.release(); t->d_shapes.release(); t->d_exact.release();
   t->d_vdict.release(); t->d_vdict_bytes.release(); t->d_presence.release(); t->d_all_atoms.release();
   t->d_atoms.release(); t->d_all_groups.release();
   t->d_tags.release(); t->d_slot_group.release(); t->d_groups.release(); t->d_lits.release(); t->d_rems.release(); t->d_qlist.release();
@@ -779,7 +786,7 @@ int32_t chq_host_free(void* p) {
 int32_t chq_stats(const chq_table* t, char* json, uint32_t cap) {
   if (!t || !json || !cap) return fail(CHQ_E_ARG, "chq_stats: bad argument");
   const CompiledTable& c = t->ct;
-  const uint64_t table_bytes = c.dict.size() * sizeof(DictSlot) + c.dict_bytes.size() + c.shapes.size() * sizeof(Shape) +
+  const uint64_t table_bytes = c.dict.size() * sizeof(DictSlot) + c.dict_bytes.size() + c.wdict.size() * (sizeof(WordSlot) + 4) + c.shapes.size() * sizeof(Shape) +
                                c.tags.size() * 2 + c.slot_group.size() * 4 + c.groups.size() * sizeof(Group) +
                                (c.lits.size() + c.rems.size() + c.qlist.size()) * 4;
   int w = snprintf(json, cap,
@@ -793,33 +800,45 @@ int32_t chq_stats(const chq_table* t, char* json, uint32_t cap) {
   return (w < 0 || (uint32_t)w >= cap) ? fail(CHQ_E_ARG, "chq_stats: buffer too small") : CHQ_OK;
 }
 
-int32_t chq_profile(chq_table* t, int32_t enable, double* tokenize_ms, double* route_ms, uint32_t* launches) {
-  if (!t) return fail(CHQ_E_ARG, "chq_profile: bad argument");
-  if (t->host_only) return fail(CHQ_E_CUDA, "chq_profile: host-only table");
+static int32_t profile_collect(chq_table* t, int32_t enable, double ms[4], uint32_t* launches, const char* who) {
+  if (!t) return fail(CHQ_E_ARG, std::string(who) + ": bad argument");
+  if (t->host_only) return fail(CHQ_E_CUDA, std::string(who) + ": host-only table");
   int rc = set_device(t);
   if (rc) return rc;
   CU(cudaDeviceSynchronize());
-  double tk = 0, rt = 0;
   uint32_t cnt = 0;
+  for (int k = 0; k < 4; ++k) ms[k] = 0;
   Workspace* all[CHQ_SLOTS + 1];
   for (int i = 0; i < CHQ_SLOTS; ++i) all[i] = &t->slots[i].ws;
   all[CHQ_SLOTS] = &t->dev_ws;
   for (Workspace* ws : all) {
     for (int i = 0; i < ws->prof_n; ++i) {
-      float a = 0, b = 0;
-      CU(cudaEventElapsedTime(&a, ws->ev[i][0], ws->ev[i][1]));
-      CU(cudaEventElapsedTime(&b, ws->ev[i][1], ws->ev[i][2]));
-      tk += a;
-      rt += b;
+      for (int k = 0; k < 4; ++k) {
+        float a = 0;
+        CU(cudaEventElapsedTime(&a, ws->ev[i][k], ws->ev[i][k + 1]));
+        ms[k] += a;
+      }
       ++cnt;
     }
     ws->prof_n = 0;
   }
-  if (tokenize_ms) *tokenize_ms = tk;
-  if (route_ms) *route_ms = rt;
   if (launches) *launches = cnt;
   t->profile = enable != 0;
   return CHQ_OK;
+}
+
+int32_t chq_profile(chq_table* t, int32_t enable, double* tokenize_ms, double* route_ms, uint32_t* launches) {
+  double ms[4];
+  int rc = profile_collect(t, enable, ms, launches, "chq_profile");
+  if (rc) return rc;
+  if (tokenize_ms) *tokenize_ms = ms[0];
+  if (route_ms) *route_ms = ms[1] + ms[2] + ms[3];
+  return CHQ_OK;
+}
+
+int32_t chq_profile_kernels(chq_table* t, int32_t enable, double* kernel_ms, uint32_t* launches) {
+  if (!kernel_ms) return fail(CHQ_E_ARG, "chq_profile_kernels: bad argument");
+  return profile_collect(t, enable, kernel_ms, launches, "chq_profile_kernels");
 }
 
 uint64_t chq_kernel_launches(void) { return kernel_launches() ; }

@@ -69,7 +69,16 @@ struct Group {            // 64 B; the first 32 B sector answers most probe hits
 // only read on a tag hit.  Built at most ~3/8 full; a bucket with an empty slot ends a probe.
 constexpr int kBucketSlots = 8;
 
-struct DictSlot {         // 32 B: one interned pattern word
+// Routing-key words (topic / direct tables): 16-byte slots so that a probe is one lane-load.  A word of
+// at most 8 bytes is identified by (first8, len) alone; longer words also compare the hash bits and
+// then the bytes kept in dict_bytes at wdict_off[slot].
+struct WordSlot {
+  uint64_t first8;        // first 8 bytes, little-endian packed, zero padded
+  uint32_t id;            // 0 = empty slot
+  uint32_t tag_len;       // word_hash & 0xFFFFFF00 | length in bytes (<= 255)
+};
+
+struct DictSlot {         // 32 B: one interned header field name / value atom (headers tables)
   uint64_t hash;
   uint64_t first8;        // first 8 bytes, little-endian packed (whole word when len <= 8)
   uint32_t len;
@@ -98,9 +107,12 @@ constexpr int kHeaderListsPerMessage = 16; // descriptor arena = this many match
 
 // Device view of a committed table (all pointers are device pointers).
 struct TableView {
-  const DictSlot* dict;
+  const DictSlot* dict;        // headers tables: field names
   const uint8_t* dict_bytes;
   uint32_t dict_mask;
+  const WordSlot* wdict;       // topic / direct tables: pattern words
+  const uint32_t* wdict_off;   // [slots] offset into dict_bytes of a word longer than 8 bytes
+  uint32_t wdict_mask;
   const Shape* shapes;
   // [3*(kLenCap+1)]: for a key of L words, rng[3L], rng[3L+1] = the kExact shapes with len == L,
   // and [hashy_begin, rng[3L+2]) = the kTail/kComplex shapes (ascending len) with len <= L
@@ -153,7 +165,20 @@ CHQ_HD uint32_t zob(uint32_t p, uint32_t w) {
   return x ^ (x >> 16);
 }
 CHQ_HD uint32_t tag16(uint32_t h) { return ((h * 0x9E3779B1u) >> 16) | 1u; }
-// FNV-1a over the word's bytes, one byte at a time so the tokeniser can fold it into its scan
+// Hash of a routing-key word: folded over its bytes eight at a time (little-endian, zero padded; an
+// empty word is one zero chunk), then the length.  The tokeniser reads keys as aligned 32-bit words, so
+// a chunk is two registers.
+constexpr uint32_t kWordBasis = 0x811C9DC5u;
+CHQ_HD uint32_t word_chunk(uint32_t h, uint32_t lo, uint32_t hi) {
+  h = (h ^ lo) * 0x9E3779B1u;
+  h = (h ^ (h >> 15) ^ hi) * 0x85EBCA77u;
+  return h ^ (h >> 13);
+}
+CHQ_HD uint32_t word_fin(uint32_t h, uint32_t len) {
+  h = (h ^ len) * 0xC2B2AE3Du;
+  return h ^ (h >> 16);
+}
+// FNV-1a, one byte at a time (header field names and values)
 constexpr uint64_t kFnvBasis = 0xCBF29CE484222325ull;
 constexpr uint64_t kFnvPrime = 0x100000001B3ull;
 CHQ_HD uint64_t fnv_step(uint64_t h, uint8_t b) { return (h ^ b) * kFnvPrime; }

@@ -93,6 +93,8 @@ uint64_t value_atom_hash(uint32_t name_id, uint8_t tag, std::string_view value) 
 void HostTable::compile_headers(CompiledTable& out) const {
   out.headers_mode = true;
   out.wstride = 4;
+  out.wdict.assign(1, WordSlot{});
+  out.wdict_off.assign(1, 0);
   out.tags.assign(kBucketSlots, 0);
   out.slot_group.assign(kBucketSlots, kNone);
   out.groups.assign(1, Group{});

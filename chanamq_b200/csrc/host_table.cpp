@@ -68,10 +68,19 @@ int HostTable::unbind_queue(std::string_view queue) {
 
 namespace {
 
-uint64_t word_hash(std::string_view w) {
-  uint64_t h = kFnvBasis;
-  for (unsigned char c : w) h = fnv_step(h, c);
-  return fin(h ^ ((uint64_t)w.size() << 56));
+uint32_t chunk32(std::string_view w, size_t at) {  // four bytes from `at`, little-endian, zero padded
+  uint32_t v = 0;
+  for (size_t i = 0; i < 4 && at + i < w.size(); ++i) v |= (uint32_t)(unsigned char)w[at + i] << (8 * i);
+  return v;
+}
+uint32_t word_hash(std::string_view w) {  // the tokeniser computes the same from aligned loads (kernels.cu)
+  uint32_t h = kWordBasis;
+  size_t at = 0;
+  do {
+    h = word_chunk(h, chunk32(w, at), chunk32(w, at + 4));
+    at += 8;
+  } while (at < w.size());
+  return word_fin(h, (uint32_t)w.size());
 }
 uint64_t first8(std::string_view w) {
   uint64_t f = 0;
@@ -118,6 +127,8 @@ void HostTable::compile(CompiledTable& out) const {
 
   if (type_ == CHQ_FANOUT) {  // FanoutMatcher.lookup: every subscriber (QueueMatcher.scala:63-65)
     out.dict.assign(1, DictSlot{});
+    out.wdict.assign(1, WordSlot{});
+    out.wdict_off.assign(1, 0);
     out.tags.assign(kBucketSlots, 0);
     out.slot_group.assign(kBucketSlots, kNone);
     if (!live_.empty()) {
@@ -327,18 +338,22 @@ void HostTable::compile(CompiledTable& out) const {
 
   // word dictionary (open addressing on the word hash, at most half full)
   uint32_t nd = pow2_at_least(std::max<uint64_t>(2, words.size() * 2));
-  out.dict.assign(nd, DictSlot{});
+  out.dict.assign(1, DictSlot{});
+  out.wdict.assign(nd, WordSlot{});
+  out.wdict_off.assign(nd, 0);
   for (auto& kv : words) {
-    DictSlot s{};
-    s.hash = word_hash(kv.first);
+    const uint32_t h = word_hash(kv.first);
+    WordSlot s{};
     s.first8 = first8(kv.first);
-    s.len = (uint32_t)kv.first.size();
     s.id = kv.second;
-    s.byte_off = (uint32_t)out.dict_bytes.size();
-    if (kv.first.size() > 8) out.dict_bytes.insert(out.dict_bytes.end(), kv.first.begin(), kv.first.end());
-    uint32_t i = (uint32_t)s.hash & (nd - 1);
-    while (out.dict[i].id != 0) i = (i + 1) & (nd - 1);
-    out.dict[i] = s;
+    s.tag_len = (h & 0xFFFFFF00u) | (uint32_t)kv.first.size();
+    uint32_t i = h & (nd - 1);
+    while (out.wdict[i].id != 0) i = (i + 1) & (nd - 1);
+    out.wdict[i] = s;
+    if (kv.first.size() > 8) {
+      out.wdict_off[i] = (uint32_t)out.dict_bytes.size();
+      out.dict_bytes.insert(out.dict_bytes.end(), kv.first.begin(), kv.first.end());
+    }
   }
   if (out.dict_bytes.empty()) out.dict_bytes.push_back(0);
 }

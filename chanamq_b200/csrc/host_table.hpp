@@ -17,8 +17,10 @@
 namespace chq {
 
 struct CompiledTable {
-  std::vector<DictSlot> dict;
+  std::vector<DictSlot> dict;          // header field names (headers tables)
   std::vector<uint8_t> dict_bytes;
+  std::vector<WordSlot> wdict;         // pattern words (topic / direct tables)
+  std::vector<uint32_t> wdict_off;
   std::vector<Shape> shapes;
   std::vector<uint16_t> exact_rng;
   uint32_t hashy_begin = 0, hashy_end = 0;

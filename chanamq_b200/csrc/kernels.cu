@@ -31,41 +31,111 @@
 
 namespace chq {
 
-// One thread per key.  Java split semantics: words are cut at every '.', trailing
+// One thread per key; the threads of a warp take one WORD per loop trip, so the dictionary probe is
+// executed by all of them together.  Java split semantics: words are cut at every '.', trailing
 // empty words are dropped, a key without any '.' is one word (even when empty).
 // Key i is blob[off[i] .. off[i+1]) (klen == null: keys packed back to back) or blob[off[i] .. off[i]+klen[i])
 // (keys scattered inside a byte batch, as the frame decoder leaves them).
-__global__ void __launch_bounds__(256) k_tokenize(const uint8_t* __restrict__ blob, const uint32_t* __restrict__ off,
-                                                  const uint32_t* __restrict__ klen, uint32_t n, TableView tv, int split,
-                                                  uint32_t* __restrict__ wid, uint8_t* __restrict__ nwords,
-                                                  uint8_t* __restrict__ err) {
+// Bytes are fetched as aligned 32-bit words and shifted into place: eight key bytes = three loads that
+// mostly hit L1 (neighbouring keys share the lines).  A word that straddles the edge of the readable
+// range [rlo, rhi) is assembled from byte loads, so nothing outside that range is ever touched.
+constexpr int kTokThreads = 256;
+constexpr int kTokStage = 8;   // rows of up to this many word ids are staged in shared memory and stored coalesced
+
+__device__ __forceinline__ uint32_t key_word32(const uint32_t* __restrict__ ab, uint32_t k, uint32_t rlo, uint32_t rhi) {
+  const uint32_t lo = 4 * k;
+  if (lo >= rhi) return 0;
+  if (lo >= rlo && lo + 4 <= rhi) return __ldg(ab + k);
+  uint32_t w = 0;
+  const uint8_t* b = reinterpret_cast<const uint8_t*>(ab);
+#pragma unroll
+  for (uint32_t j = 0; j < 4; ++j)
+    if (lo + j >= rlo && lo + j < rhi) w |= (uint32_t)__ldg(b + lo + j) << (8 * j);
+  return w;
+}
+// 0x80 in every byte of x that equals '.'
+__device__ __forceinline__ uint32_t dot_bytes(uint32_t x) {
+  x ^= 0x2E2E2E2Eu;
+  return (x - 0x01010101u) & ~x & 0x80808080u;
+}
+
+__global__ void __launch_bounds__(kTokThreads) k_tokenize(const uint8_t* __restrict__ blob, const uint32_t* __restrict__ off,
+                                                          const uint32_t* __restrict__ klen, uint32_t n, TableView tv, int split,
+                                                          uint32_t* __restrict__ wid, uint8_t* __restrict__ nwords,
+                                                          uint8_t* __restrict__ err) {
+  __shared__ uint32_t stage[kTokThreads][kTokStage + 1];
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const uint32_t b0 = off[i], b1 = klen ? b0 + klen[i] : off[i + 1];
-  if (b1 - b0 > (uint32_t)kMaxKeyBytes) { nwords[i] = 0; err[i] = 2; return; }
+  const int lane = threadIdx.x & 31;
+  const bool staged = tv.wstride <= (uint32_t)kTokStage;
+  // byte offsets below are relative to the 4-byte aligned address at or before blob
+  const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(blob) & 3u);
+  const uint32_t* ab = reinterpret_cast<const uint32_t*>(blob - mis);
+  uint32_t v0 = 0, v1 = 0, rlo = 0, rhi = 0;
+  bool active = i < n;
+  if (active) {
+    const uint32_t b0 = off[i], b1 = klen ? b0 + klen[i] : off[i + 1];
+    v0 = b0 + mis; v1 = b1 + mis;
+    if (klen) { rlo = v0; rhi = v1; }                 // scattered keys: stay inside this key
+    else { rlo = mis; rhi = __ldg(off + n) + mis; }   // packed keys: stay inside the blob
+    if (b1 - b0 > (uint32_t)kMaxKeyBytes) { nwords[i] = 0; err[i] = 2; active = false; }
+  }
+  if (staged) {
+#pragma unroll
+    for (int c = 0; c < kTokStage; ++c) stage[threadIdx.x][c] = 0;
+  }
   uint32_t* row = wid + (size_t)i * tv.wstride;
-  uint32_t cnt = 0, last_nonempty = 0, wl = 0, wstart = b0;
+  const bool live = active;
+  uint32_t cnt = 0, last_nonempty = 0, pos = v0;
   bool dot = false;
-  uint64_t h = kFnvBasis, f8 = 0;
-  for (uint32_t j = b0; j <= b1; ++j) {
-    const bool end = (j == b1);
-    const uint8_t c = end ? 0 : __ldg(blob + j);
-    if (end || (split && c == '.')) {
-      const uint32_t id = dict_lookup(tv, h, f8, wl, blob + wstart);
-      if (cnt < tv.wstride) row[cnt] = id;
-      ++cnt;
-      if (wl > 0) last_nonempty = cnt;
-      if (!end) dot = true;
-      h = kFnvBasis; f8 = 0; wl = 0; wstart = j + 1;
-    } else {
-      h = fnv_step(h, c);
-      if (wl < 8) f8 |= (uint64_t)c << (8 * wl);
-      ++wl;
+  while (active) {
+    // one word: bytes from pos up to the next '.' or the end of the key, eight at a time
+    uint32_t h = kWordBasis, wl = 0, f_lo = 0, f_hi = 0;
+    bool ends_with_dot = false;
+    for (uint32_t q = pos;; q += 8) {
+      const uint32_t k = q >> 2, sh = (q & 3u) * 8u;
+      const uint32_t w0 = key_word32(ab, k, rlo, rhi), w1 = key_word32(ab, k + 1, rlo, rhi);
+      const uint32_t w2 = sh ? key_word32(ab, k + 2, rlo, rhi) : 0u;
+      uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+      const uint32_t rem = v1 - q;
+      uint32_t p = 8;
+      if (split) {
+        const uint32_t dl = dot_bytes(lo), dh = dot_bytes(hi);
+        p = dl ? (uint32_t)(__ffs(dl) - 1) >> 3 : (dh ? 4u + ((uint32_t)(__ffs(dh) - 1) >> 3) : 8u);
+      }
+      const uint32_t lim = min(rem, 8u), take = min(p, lim);
+      if (take < 8) {
+        if (take >= 4) hi &= (1u << (8 * (take - 4))) - 1u;
+        else { hi = 0; lo &= (1u << (8 * take)) - 1u; }
+      }
+      if (q == pos) { f_lo = lo; f_hi = hi; }
+      if (take > 0 || q == pos) h = word_chunk(h, lo, hi);
+      wl += take;
+      if (take < 8) { ends_with_dot = p < lim; break; }
+    }
+    const uint32_t id = word_lookup(tv, word_fin(h, wl), f_lo, f_hi, wl, blob + (pos - mis));
+    if (cnt < tv.wstride) {
+      if (staged) stage[threadIdx.x][cnt] = id;
+      else row[cnt] = id;
+    }
+    ++cnt;
+    if (wl > 0) last_nonempty = cnt;
+    if (ends_with_dot) { dot = true; pos += wl + 1; }
+    else active = false;
+  }
+  if (live) {
+    const uint32_t nw = dot ? last_nonempty : 1;
+    nwords[i] = (uint8_t)nw;
+    err[i] = nw == 0 ? 1 : 0;
+  }
+  if (staged) {  // 32 rows of a warp are contiguous in wid: store them as whole lines
+    __syncwarp();
+    const uint32_t ws = tv.wstride, tbase = threadIdx.x - lane;
+    const uint32_t first = blockIdx.x * blockDim.x + tbase;     // first key of this warp
+    for (uint32_t x = lane; x < 32 * ws; x += 32) {
+      const uint32_t r = x / ws, c = x - r * ws;
+      if (first + r < n) wid[(size_t)first * ws + x] = stage[tbase + r][c];
     }
   }
-  const uint32_t nw = dot ? last_nonempty : 1;
-  nwords[i] = (uint8_t)nw;
-  err[i] = nw == 0 ? 1 : 0;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -506,7 +576,7 @@ void note_launches(int n) { g_launches += (unsigned long long)n; }
 cudaError_t launch_tokenize(const uint8_t* blob, const uint32_t* off, uint32_t n, const TableView& tv, int split,
                             uint32_t* wid, uint8_t* nwords, uint8_t* err, cudaStream_t st) {
   if (n == 0) return cudaSuccess;
-  k_tokenize<<<(n + 255) / 256, 256, 0, st>>>(blob, off, nullptr, n, tv, split, wid, nwords, err);
+  k_tokenize<<<(n + kTokThreads - 1) / kTokThreads, kTokThreads, 0, st>>>(blob, off, nullptr, n, tv, split, wid, nwords, err);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -514,7 +584,7 @@ cudaError_t launch_tokenize(const uint8_t* blob, const uint32_t* off, uint32_t n
 cudaError_t launch_tokenize_keys(const uint8_t* bytes, const uint32_t* key_off, const uint32_t* key_len, uint32_t n,
                                  const TableView& tv, int split, uint32_t* wid, uint8_t* nwords, uint8_t* err, cudaStream_t st) {
   if (n == 0) return cudaSuccess;
-  k_tokenize<<<(n + 255) / 256, 256, 0, st>>>(bytes, key_off, key_len, n, tv, split, wid, nwords, err);
+  k_tokenize<<<(n + kTokThreads - 1) / kTokThreads, kTokThreads, 0, st>>>(bytes, key_off, key_len, n, tv, split, wid, nwords, err);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -531,7 +601,7 @@ cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t 
   return cudaGetLastError();
 }
 
-cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st) {
+cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st, cudaEvent_t* between) {
   if (p.n == 0) return cudaSuccess;
   static int occ_by_dev[64] = {};
   int dev = 0;
@@ -544,7 +614,9 @@ cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st) {
     if (occ < 1) occ = 1;
   }
   k_probe<<<(p.n + kRouteThreads - 1) / kRouteThreads, kRouteThreads, sizeof(RouteSmem), st>>>(p);
+  if (between && (e = cudaEventRecord(between[0], st)) != cudaSuccess) return e;
   k_offsets<<<p.n_tiles, kScanThreads, 0, st>>>(p);
+  if (between && (e = cudaEventRecord(between[1], st)) != cudaSuccess) return e;
   const uint64_t want = (uint64_t)n_sms * occ, chunks = (p.n + 31) / 32;
   k_write<<<(uint32_t)(chunks < want ? chunks : want), kRouteThreads, 0, st>>>(p);
   g_launches += 3;

@@ -64,7 +64,8 @@ void note_launches(int n);
 cudaError_t launch_headers_match(const uint8_t* blob, const uint32_t* off, const uint32_t* hlen, uint32_t n, const TableView& tv,
                                  uint32_t* desc_k, uint32_t* desc_start, uint8_t* desc_flags, uint2* desc_lists, uint32_t arena_cap,
                                  uint32_t* arena_used, uint32_t* status_word, uint8_t* err, cudaStream_t st);
-cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st);
+// between: optional two events, recorded after k_probe and after k_offsets (per-kernel timing)
+cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st, cudaEvent_t* between = nullptr);
 cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t st);
 unsigned long long kernel_launches();
 

@@ -43,6 +43,27 @@ __device__ uint32_t dict_lookup(const TableView& tv, uint64_t fnv, uint64_t f8, 
   }
 }
 
+// Routing-key word -> id (topic / direct tables): one 16-byte load per probe step.  h = word_fin(...),
+// (lo, hi) = the first 8 bytes, bytes = the whole word (read only to confirm a word longer than 8 bytes).
+__device__ __forceinline__ uint32_t word_lookup(const TableView& tv, uint32_t h, uint32_t lo, uint32_t hi, uint32_t len,
+                                                const uint8_t* bytes) {
+  const uint32_t want = (h & 0xFFFFFF00u) | len;
+  uint32_t i = h & tv.wdict_mask;
+  for (;;) {
+    const uint4 a = ldg16(&tv.wdict[i]);
+    if (a.z == 0) return kUnknownWord;
+    if (a.x == lo && a.y == hi && a.w == want) {
+      if (len <= 8) return a.z;
+      const uint8_t* d = tv.dict_bytes + __ldg(tv.wdict_off + i);
+      bool same = true;
+      for (uint32_t j = 8; j < len; ++j)
+        if (__ldg(d + j) != __ldg(bytes + j)) { same = false; break; }
+      if (same) return a.z;
+    }
+    i = (i + 1) & tv.wdict_mask;
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // table records
 // ------------------------------------------------------------------------------------------

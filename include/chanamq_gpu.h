@@ -127,8 +127,8 @@ int32_t chq_route_device(chq_table* t, const uint8_t* d_keys_blob, const uint32_
  * and would get cudaErrorMemoryAllocation from a fresh request; a deployment whose rule is that
  * nothing is allocated after start-up, so that steady-state routing can never fail for lack of memory.
  *
- * The scratch the two launches need (prefix-sum state, the interned word ids of the batch, the arena
- * of the rare merge slow path) sits in one fixed array inside the library image: about 6.3 MiB of
+ * The scratch the launches need (prefix-sum state, the interned word ids and list descriptors of the batch, the arena
+ * of the rare merge slow path) sits in one fixed array inside the library image: about 11 MiB of
  * device memory on every GPU that loads libchanagpu.so, held until the process exits.  Hence the limits:
  *   n                        <= CHQ_STATIC_MAX_KEYS  (65 536 keys per call)
  *   n x the table's word stride <= CHQ_STATIC_MAX_WORDS (524 288; the stride is 8 for ordinary tables,
@@ -222,9 +222,12 @@ int32_t chq_host_free(void* p);
  * ids, device bytes of the table */
 int32_t chq_stats(const chq_table* t, char* json, uint32_t cap);
 /* Per-kernel device time, measured with CUDA events recorded on the launching stream around k_tokenize
- * and k_route.  The call synchronises the device, returns the sums (ms) and the number of batches since
- * the last call (at most 256 are kept), then switches recording on or off. */
+ * and the route kernels (k_probe + k_offsets + k_write).  The call synchronises the device, returns the
+ * sums (ms) and the number of batches since the last call (at most 256 are kept), then switches recording
+ * on or off. */
 int32_t chq_profile(chq_table* t, int32_t enable, double* tokenize_ms, double* route_ms, uint32_t* launches);
+/* The same, one sum per kernel: kernel_ms[0..3] = k_tokenize (or k_headers_match), k_probe, k_offsets, k_write. */
+int32_t chq_profile_kernels(chq_table* t, int32_t enable, double* kernel_ms, uint32_t* launches);
 /* how many of this library's kernels have been launched by this process (all tables) */
 uint64_t chq_kernel_launches(void);
 /* test hook: lower the per-message limits that select the slower merge paths (0 = default) */
