@@ -74,6 +74,7 @@ def load_library():
         "chq_profile_kernels": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(u32)]),
         "chq_kernel_launches": (u64, []),
         "chq_debug_limits": (i32, [vp, u32, u32]),
+        "chq_debug_clocks": (i32, [C.POINTER(C.c_uint64)]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)

@@ -843,6 +843,14 @@ int32_t chq_profile_kernels(chq_table* t, int32_t enable, double* kernel_ms, uin
 
 uint64_t chq_kernel_launches(void) { return kernel_launches() ; }
 
+int32_t chq_debug_clocks(uint64_t* out32) {
+  if (!out32) return fail(CHQ_E_ARG, "chq_debug_clocks: bad argument");
+  CU(cudaDeviceSynchronize());
+  static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "");
+  CU(read_clocks(reinterpret_cast<unsigned long long*>(out32)));
+  return CHQ_OK;
+}
+
 int32_t chq_debug_limits(chq_table* t, uint32_t max_slots, uint32_t max_small) {
   if (!t) return fail(CHQ_E_ARG, "chq_debug_limits: bad argument");
   t->max_slots = (max_slots == 0 || max_slots > (uint32_t)kRouteSlots) ? kRouteSlots : max_slots;

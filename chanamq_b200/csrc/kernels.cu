@@ -141,6 +141,26 @@ __global__ void __launch_bounds__(kTokThreads) k_tokenize(const uint8_t* __restr
 // ------------------------------------------------------------------------------------------
 // the fused route kernel
 // ------------------------------------------------------------------------------------------
+// Optional cycle accounting of k_write by kind of message (build with CHQ_NVCC_DEFS=-DCHQ_CLOCKS; read with
+// chq_debug_clocks): [8*0 + b] cycles, [8*1 + b] messages, [8*2 + b] ids of bin b
+// (0 sweep for big messages, 1 tiny, 2 single list, 3 slow-path copy, 4 multi-way, 5 weave <= 32 short ids,
+// 6 weave > 32 short ids, 7 per-chunk header loads).
+#ifdef CHQ_CLOCKS
+__device__ unsigned long long g_clk[32];
+#define CHQ_CLK_T0() const long long clk_t0 = clock64()
+#define CHQ_CLK_ADD(bin, msgs, ids)                                              \
+  do {                                                                           \
+    if ((threadIdx.x & 31) == 0) {                                               \
+      atomicAdd(&g_clk[bin], (unsigned long long)(clock64() - clk_t0));          \
+      atomicAdd(&g_clk[8 + (bin)], (unsigned long long)(msgs));                  \
+      atomicAdd(&g_clk[16 + (bin)], (unsigned long long)(ids));                  \
+    }                                                                            \
+  } while (0)
+#else
+#define CHQ_CLK_T0() do {} while (0)
+#define CHQ_CLK_ADD(bin, msgs, ids) do {} while (0)
+#endif
+
 namespace {
 
 constexpr int kWarps = kRouteThreads / 32;
@@ -297,6 +317,8 @@ __device__ uint32_t warp_fallback_lists(const RouteParams& p, uint32_t my_off, u
 namespace {
 
 constexpr uint32_t kMetaTiny = 1u << 13, kMetaDedup = 1u << 12;  // meta = k | class << 8 | flags
+constexpr uint32_t kMetaBig = 1u << 14;   // long result: k_write starts these first so that none is left for the end
+constexpr uint32_t kBigIds = 1024;
 
 }  // namespace
 
@@ -372,7 +394,8 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
       }
     }
   }
-  // classify: 0 = count known, 1 = needs the de-duplicating merge to count, 2 = slow path (result parked in scratch)
+  // classify: 0 = count known, 1 = needs the de-duplicating merge to count, 2 = slow path (result parked in
+  // scratch), 3 = count known, several long lists (k_write merges them with warp_union_long)
   int cls = 0;
   const bool dedup = (flags & kShared) != 0;
   // tiny: the whole result fits the 16-input sorting network of one thread (merge.cuh)
@@ -382,7 +405,8 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   if (tiny) cnt = (k == 1 || !dedup) ? ub : tiny_union(tv.qlist, k, my_off, my_len, nullptr);
   else if (overflow) cls = 2;
   else if (k <= 1) cnt = ub;
-  else if (k > p.max_slots || ub - mxlen > p.max_small) cls = 2;
+  else if (k > p.max_slots || (dedup && ub - mxlen > p.max_small)) cls = 2;
+  else if (ub - mxlen > p.max_small) { cls = 3; cnt = ub; }
   else if (dedup) cls = 1;
   else cnt = ub;
 
@@ -419,7 +443,8 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   if (m >= p.n) return;
   p.durable[m] = (flags & kAnyDurable) ? 1 : 0;
   p.cnt[m] = cnt;
-  p.meta[m] = min(k, 255u) | ((uint32_t)cls << 8) | (dedup ? kMetaDedup : 0u) | (tiny ? kMetaTiny : 0u);
+  p.meta[m] = min(k, 255u) | ((uint32_t)cls << 8) | (dedup ? kMetaDedup : 0u) | (tiny ? kMetaTiny : 0u) |
+              ((cls == 3 || cnt >= kBigIds) ? kMetaBig : 0u);
   uint2* lists = p.mlist + (size_t)m * kRouteSlots;
   if (cls == 2) {
     lists[0] = make_uint2((uint32_t)scr, (uint32_t)(scr >> 32));
@@ -511,6 +536,49 @@ __global__ void __launch_bounds__(kScanThreads) k_offsets(RouteParams p) {
   }
 }
 
+// One message, by the whole warp: c ids to ids[o ...), described by its meta word mt and its row of lists.
+// k_write has ONE call site for it (both passes share the loop) so that the kernel stays inside the
+// instruction cache.
+struct WriteCtx {  // the few fields of RouteParams it needs, by value (kernel parameters have no address)
+  const uint32_t* qlist;
+  const uint2* mlist;
+  const uint32_t* scratch;
+  uint32_t* ids;
+  uint64_t ids_cap;
+};
+__device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws, uint32_t mm, uint32_t c, uint32_t mt,
+                                           uint64_t o, int lane) {
+  const int kk = mt & 0xFF, cl = (mt >> 8) & 0xF;
+  const uint2* ml = p.mlist + (size_t)mm * kRouteSlots;
+  CHQ_CLK_T0();
+  if (cl == 2) {
+    const uint2 s2 = __ldg(ml);
+    const uint64_t so = ((uint64_t)s2.y << 32) | s2.x;
+    for (uint32_t i = lane; i < c; i += 32) p.ids[o + i] = p.scratch[so + i];
+    CHQ_CLK_ADD(3, 1, c);
+  } else if (kk == 1) {
+    const uint32_t* sp = p.qlist + __ldg(ml).x + lane;
+    uint32_t* dst = p.ids + o + lane;
+    uint32_t i = lane;
+    for (; i + 96 < c; i += 128, sp += 128, dst += 128) {
+      const uint32_t v0 = __ldg(sp), v1 = __ldg(sp + 32), v2 = __ldg(sp + 64), v3 = __ldg(sp + 96);
+      dst[0] = v0; dst[32] = v1; dst[64] = v2; dst[96] = v3;
+    }
+    for (; i < c; i += 32, sp += 32, dst += 32) *dst = __ldg(sp);
+    CHQ_CLK_ADD(2, 1, c);
+  } else {
+    uint32_t lo = 0, ll = 0;
+    if (lane < kk) { const uint2 d = __ldg(ml + lane); lo = d.x; ll = d.y; }
+    if (cl == 3) warp_union_long(p.qlist, lo, ll, kk, ws, p.ids, o, lane);
+    else warp_union<true>(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, p.ids_cap, lane);
+#ifdef CHQ_CLOCKS
+    uint32_t sum = ll, mx = ll;
+    for (int d = 16; d; d >>= 1) { sum += __shfl_xor_sync(kFull, sum, d); mx = max(mx, __shfl_xor_sync(kFull, mx, d)); }
+    CHQ_CLK_ADD(cl == 3 ? 4 : (sum - mx <= 32 ? 5 : 6), 1, c);
+#endif
+  }
+}
+
 __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RouteParams p) {
   __shared__ WarpScratch ws_all[kRouteThreads / 32];
   const TableView& tv = p.tv;
@@ -518,49 +586,51 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RoutePa
   WarpScratch& ws = ws_all[warp];
   const uint32_t n_chunks = (p.n + 31) / 32;
   if (*p.total > 0xFFFFFFFFull || (p.debug & 1u)) return;  // offsets saturated: the launch reports CHQ_E_OVERFLOW
-  for (;;) {
-    uint32_t chunk = 0;
-    if (lane == 0) chunk = atomicAdd(p.ctrl + kCtrlChunk, 1u);  // 32 consecutive messages per grab
-    chunk = __shfl_sync(kFull, chunk, 0);
-    if (chunk >= n_chunks) return;
-    const uint32_t m = chunk * 32 + lane;
-    uint32_t cnt = 0, meta = 0, pos = 0;
-    if (m < p.n) {
-      cnt = p.cnt[m];
-      meta = p.meta[m];
-      pos = p.offsets[m];
-    }
-    const bool fits = (uint64_t)pos + cnt <= p.ids_cap;  // else CHQ_E_OVERFLOW: nothing is written past ids_cap
-    const uint2* lists = p.mlist + (size_t)m * kRouteSlots;
-    if ((meta & kMetaTiny) && cnt > 0 && fits) {  // tiny messages: their own lane gathers, sorts and writes
-      auto off = [&](uint32_t j) { return __ldg(lists + j).x; };
-      auto len = [&](uint32_t j) { return __ldg(lists + j).y; };
-      tiny_union(tv.qlist, meta & 0xFF, off, len, p.ids + pos);
-    }
-    __syncwarp();
-    for (unsigned todo = __ballot_sync(kFull, cnt > 0 && fits && !(meta & kMetaTiny)); todo; todo &= todo - 1) {
-      const int src = __ffs(todo) - 1;
-      const uint32_t c = __shfl_sync(kFull, cnt, src), mt = __shfl_sync(kFull, meta, src);
-      const uint64_t o = __shfl_sync(kFull, pos, src);
-      const int kk = mt & 0xFF, cl = (mt >> 8) & 0xF;
-      const uint2* ml = p.mlist + (size_t)(chunk * 32 + src) * kRouteSlots;
-      if (cl == 2) {
-        const uint2 s2 = __ldg(ml);
-        const uint64_t so = ((uint64_t)s2.y << 32) | s2.x;
-        for (uint32_t i = lane; i < c; i += 32) p.ids[o + i] = p.scratch[so + i];
-      } else if (kk == 1) {
-        const uint32_t* sp = tv.qlist + __ldg(ml).x + lane;
-        uint32_t* dst = p.ids + o + lane;
-        uint32_t i = lane;
-        for (; i + 96 < c; i += 128, sp += 128, dst += 128) {
-          const uint32_t v0 = __ldg(sp), v1 = __ldg(sp + 32), v2 = __ldg(sp + 64), v3 = __ldg(sp + 96);
-          dst[0] = v0; dst[32] = v1; dst[64] = v2; dst[96] = v3;
+  const WriteCtx wc{tv.qlist, p.mlist, p.scratch, p.ids, p.ids_cap};
+  // Two passes over the batch, 32 consecutive messages per sub-chunk.  Pass 0 sweeps the meta words (four
+  // sub-chunks per grab) and does only the few messages with long results, so that the longest jobs start
+  // first instead of being met by chance near the end of the kernel; pass 1 does everything else.
+#pragma unroll 1
+  for (int pass = 0; pass < 2; ++pass) {
+    const uint32_t span = pass == 0 ? 4u : 1u;
+    for (;;) {
+      CHQ_CLK_T0();
+      uint32_t g = 0;
+      if (lane == 0) g = atomicAdd(p.ctrl + (pass == 0 ? kCtrlBig : kCtrlChunk), 1u);
+      g = __shfl_sync(kFull, g, 0);
+      if ((uint64_t)g * span >= n_chunks) break;
+#pragma unroll 1
+      for (uint32_t q = 0; q < span; ++q) {
+        const uint32_t base = (g * span + q) * 32;
+        if (base >= p.n) break;
+        const uint32_t m = base + lane;
+        uint32_t cnt = 0, meta = 0, pos = 0;
+        if (m < p.n) {
+          meta = p.meta[m];
+          if (pass == 1 || (meta & kMetaBig)) { cnt = p.cnt[m]; pos = p.offsets[m]; }
         }
-        for (; i < c; i += 32, sp += 32, dst += 32) *dst = __ldg(sp);
-      } else {
-        uint32_t lo = 0, ll = 0;
-        if (lane < kk) { const uint2 d = __ldg(ml + lane); lo = d.x; ll = d.y; }
-        warp_union<true>(tv.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, p.ids_cap, lane);
+        const bool fits = (uint64_t)pos + cnt <= p.ids_cap;  // else CHQ_E_OVERFLOW: nothing is written past ids_cap
+        CHQ_CLK_ADD(pass == 0 ? 0 : 7, 0, 0);
+        if (pass == 1) {
+          CHQ_CLK_T0();
+          if ((meta & kMetaTiny) && cnt > 0 && fits) {  // tiny messages: their own lane gathers, sorts and writes
+            const uint2* lists = p.mlist + (size_t)m * kRouteSlots;
+            auto off = [&](uint32_t j) { return __ldg(lists + j).x; };
+            auto len = [&](uint32_t j) { return __ldg(lists + j).y; };
+            tiny_union(tv.qlist, meta & 0xFF, off, len, p.ids + pos);
+          }
+          __syncwarp();
+          const uint32_t n_tiny = __popc(__ballot_sync(kFull, (meta & kMetaTiny) && cnt > 0));
+          (void)n_tiny;
+          CHQ_CLK_ADD(1, n_tiny, 0);
+        }
+        const bool big = (meta & kMetaBig) != 0;
+        const bool sel = cnt > 0 && fits && !(meta & kMetaTiny) && (pass == 0 ? big : !big);
+        for (unsigned todo = __ballot_sync(kFull, sel); todo; todo &= todo - 1) {
+          const int src = __ffs(todo) - 1;
+          write_message(wc, ws, base + src, __shfl_sync(kFull, cnt, src), __shfl_sync(kFull, meta, src),
+                        __shfl_sync(kFull, pos, src), lane);
+        }
       }
     }
   }
@@ -593,6 +663,19 @@ cudaError_t launch_tokenize_keys(const uint8_t* bytes, const uint32_t* key_off, 
 __global__ void k_finish(const uint32_t* ctrl, int32_t* status) {
   const uint32_t s = ctrl[kCtrlStatus];
   *status = (s & kStatusScratch) ? CHQ_E_SCRATCH : (s & kStatusOverflow) ? CHQ_E_OVERFLOW : CHQ_OK;
+}
+
+// cycle accounting (zeros unless built with -DCHQ_CLOCKS); reading resets the counters
+cudaError_t read_clocks(unsigned long long* out32) {
+  for (int i = 0; i < 32; ++i) out32[i] = 0;
+#ifdef CHQ_CLOCKS
+  cudaError_t e = cudaMemcpyFromSymbol(out32, g_clk, sizeof(unsigned long long) * 32);
+  if (e != cudaSuccess) return e;
+  static const unsigned long long zero[32] = {};
+  return cudaMemcpyToSymbol(g_clk, zero, sizeof(zero));
+#else
+  return cudaSuccess;
+#endif
 }
 
 cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t st) {

@@ -17,7 +17,8 @@ constexpr int kRouteSmall = CHQ_ROUTE_SMALL;     // ids (all lists but the longe
 
 // control words (device): zeroed before every launch
 constexpr int kCtrlTile = 0 /* scan tile counter */, kCtrlStatus = 1, kCtrlScratchLo = 2 /* u64 bump pointer */,
-              kCtrlChunk = 4 /* write-kernel work counter */, kCtrlDescBump = 5 /* headers descriptor arena */, kCtrlWords = 8;
+              kCtrlChunk = 4 /* write-kernel work counter */, kCtrlDescBump = 5 /* headers descriptor arena */,
+              kCtrlBig = 6 /* write-kernel counter of its first pass (big messages) */, kCtrlWords = 8;
 constexpr int kRouteScanTile = 1024;  // counts per tile of the offsets scan
 constexpr int kStateHead = kCtrlWords / 2;  // the control words take the first kStateHead u64 of the state array
 inline uint32_t route_scan_tiles(uint32_t n) { return (n + kRouteScanTile - 1) / kRouteScanTile; }
@@ -68,5 +69,6 @@ cudaError_t launch_headers_match(const uint8_t* blob, const uint32_t* off, const
 cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st, cudaEvent_t* between = nullptr);
 cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t st);
 unsigned long long kernel_launches();
+cudaError_t read_clocks(unsigned long long* out32);
 
 }  // namespace chq

@@ -19,6 +19,7 @@ struct WarpScratch {
   uint32_t b[kRouteSmall];   // their sorted union
   uint32_t st[kRouteSlots];  // start of list j inside a[]
   uint32_t ln[kRouteSlots];  // its length (0 for the long list)
+  uint32_t win[kRouteSlots][32];  // warp_union_long: the ids each short list currently shows
 };
 
 __device__ __forceinline__ uint32_t smem_lower_bound(const uint32_t* a, uint32_t n, uint32_t x) {
@@ -359,6 +360,122 @@ __device__ uint32_t warp_union(const uint32_t* __restrict__ qlist, uint32_t my_o
   }
   __syncwarp();
   return nb + kept_total + (ns - t);
+}
+
+// Sorted union of k <= kRouteSlots sorted lists of ANY length in which no id occurs twice (lane j < k holds
+// list j = qlist[my_off .. my_off + my_len)), written to out[pos ...).  Used when the lists other than the
+// longest are too many ids for the staged paths above.
+//
+// The longest list is streamed and woven exactly as in warp_union.  The ids to weave in — the union of the
+// OTHER lists — are produced a block at a time by a multi-way step: each of those lists shows its next 32
+// ids (one per lane); ids up to T = the smallest last-shown id among the lists that still have 32 or more
+// cannot be preceded by anything unseen, so they are final: each goes to block[lane + how many shown ids of
+// the other lists are smaller] (shuffle binary searches).  The list that sets T empties its whole window, so
+// a step yields at least 32 ids (or everything that is left) and at most 32 per list.
+static_assert(2 * kRouteSmall >= 32 * (kRouteSlots - 1), "a block of short ids lives in WarpScratch::a..b");
+
+__device__ void warp_union_long(const uint32_t* __restrict__ qlist, uint32_t my_off, uint32_t my_len, int k,
+                                WarpScratch& ws, uint32_t* __restrict__ out, uint64_t pos, int lane) {
+  const uint32_t len_k = lane < k ? my_len : 0;
+  uint32_t nb = len_k;
+#pragma unroll
+  for (int d = 16; d; d >>= 1) nb = max(nb, __shfl_xor_sync(kFull, nb, d));
+  const int big = __ffs(__ballot_sync(kFull, lane < k && len_k == nb)) - 1;
+  const uint32_t big_off = __shfl_sync(kFull, my_off, big);
+  const uint32_t len_s = (lane < k && lane != big) ? my_len : 0;  // lane j: length of short list j
+  uint32_t cur = 0;                                               // lane j: ids of it already handed out
+  uint32_t* S = ws.a;                                             // the current block, ascending
+  uint32_t blk_n = 0, blk_t = 0;
+  bool more = __ballot_sync(kFull, len_s != 0) != 0;
+
+  uint32_t kept_total = 0;
+  uint32_t b_next = lane < nb ? __ldg(qlist + big_off + lane) : kNone;
+  // chunks of the long list, then one more trip (c0 == nb, no long ids, every short id in range) for what is left
+#pragma unroll 1
+  for (uint32_t c0 = 0;; c0 = min(c0 + 32, nb)) {
+    const bool tail = c0 >= nb;
+    const uint32_t i = c0 + lane;
+    const bool valid = i < nb;
+    const uint32_t b = b_next;
+    b_next = (i + 32 < nb) ? __ldg(qlist + big_off + i + 32) : kNone;
+    const uint32_t bmax = tail ? kNone - 1 : __shfl_sync(kFull, b, min(31u, nb - c0 - 1));
+    const uint32_t kept0 = kept_total;
+    uint32_t shift = 0;
+#pragma unroll 1
+    for (;;) {
+      if (blk_t == blk_n) {
+        if (!more) break;
+        // ---- next block of short ids: one multi-way step (see above) ----
+        const uint32_t rem = len_s - cur;
+        uint32_t w[kRouteSlots];
+#pragma unroll
+        for (int j = 0; j < kRouteSlots; ++j) {  // all the loads first
+          const uint32_t r = __shfl_sync(kFull, rem, j), o = __shfl_sync(kFull, my_off + cur, j);
+          w[j] = (uint32_t)lane < r ? __ldg(qlist + o + lane) : kNone;
+        }
+        uint32_t T = kNone;
+        __syncwarp();  // everyone is done with the previous block
+#pragma unroll
+        for (int j = 0; j < kRouteSlots; ++j) {
+          ws.win[j][lane] = w[j];
+          const uint32_t last = __shfl_sync(kFull, w[j], 31);
+          if (last != kNone) T = min(T, last);   // that list still has 32 or more
+        }
+        __syncwarp();
+        uint32_t emitted = 0, mine = 0;
+#pragma unroll 1
+        for (int j = 0; j < k; ++j) {
+          const uint32_t x = ws.win[j][lane];
+          const bool go = x != kNone && x <= T;
+          const uint32_t c = __popc(__ballot_sync(kFull, go));  // a prefix of the window
+          if (c == 0) continue;
+          uint32_t rank = lane;
+#pragma unroll 1
+          for (int j2 = 0; j2 < k; ++j2) {
+            const uint32_t* W = ws.win[j2];
+            if (j2 == j || W[0] == kNone) continue;
+            // shown ids of list j2 below x: at most 31 (a full window ends at or above T >= x, a partial one in kNone)
+            uint32_t q = 0;
+#pragma unroll
+            for (int step = 16; step; step >>= 1)
+              if (W[q + step - 1] < x) q += step;
+            rank += q;
+          }
+          if (go) S[rank] = x;
+          emitted += c;
+          if (lane == j) mine = c;
+        }
+        cur += mine;
+        blk_n = emitted;
+        blk_t = 0;
+        more = __ballot_sync(kFull, len_s != cur) != 0;
+        __syncwarp();
+      }
+      const uint32_t s = (blk_t + lane < blk_n) ? S[blk_t + lane] : kNone;
+      const bool inr = s <= bmax;  // in-range lanes form a prefix (the block ascends; ids < kNone)
+      const unsigned m_in = __ballot_sync(kFull, inr);
+      if (m_in == 0) break;
+      uint32_t p = 0;  // how many ids of this chunk are < s  (s <= bmax, so p <= 31; none in the last trip)
+      if (!tail) {
+#pragma unroll
+        for (int step = 16; step; step >>= 1) {
+          const uint32_t probe = __shfl_sync(kFull, b, p + step - 1);
+          if (probe < s) p += step;
+        }
+      }
+      if (inr) out[pos + c0 + p + kept_total + __popc(m_in & ((1u << lane) - 1))] = s;
+      // every long id moves up by the short ids below it
+      const uint32_t q = lanes_below(inr ? s : kNone, b);
+      shift += __popc(m_in & (q >= 32 ? kFull : ((1u << q) - 1)));
+      const uint32_t n_in = __popc(m_in);
+      kept_total += n_in;
+      blk_t += n_in;
+      if (n_in < 32 && blk_t < blk_n) break;  // the next short id lies beyond this chunk
+    }
+    if (valid) out[pos + i + kept0 + shift] = b;
+    if (tail) break;
+  }
+  __syncwarp();
 }
 
 }  // namespace

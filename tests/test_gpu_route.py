@@ -254,3 +254,77 @@ def test_slow_path_arena_grows_and_retries(monkeypatch):
     blob, off = w.keys(40_000, stream=7)
     r = assert_same_routing(m, o, blob, off, threads=4)
     assert len(r.queue_ids) > 10_000
+
+
+@pytest.mark.parametrize("mode", [CHQ_MODE_COMPAT, CHQ_MODE_SPEC])
+def test_word_lengths_around_the_8_byte_chunks(mode):
+    """the tokeniser reads keys as aligned 32-bit words and hashes eight bytes at a time: words of 0..40
+    bytes, words that only differ after byte 8 / 16, NUL and high bytes, every key alignment"""
+    rng = random.Random(77 + mode)
+    stems = [b"", b"a", b"abc", b"abcdefg", b"abcdefgh", b"abcdefghi", b"abcdefgh\x00", b"abcdefghijklmnop",
+             b"abcdefghijklmnopq", b"abcdefghijklmnoX", b"abcdefghijklmnopqrstuvwxyz0123456789-_", b"\x00", b"\x00\x00",
+             b"\xff\xfe", b"a\x00b", b"..".replace(b".", b"-"), b"#", b"*x"]
+    def topic(wild):
+        n = rng.randint(1, 6)
+        return b".".join(rng.choice(wild) if rng.random() < 0.25 else rng.choice(stems) for _ in range(n))
+    m, o = GpuMatcher(CHQ_TOPIC, mode), po.Oracle(po.TOPIC, po.SPEC if mode == CHQ_MODE_SPEC else po.COMPAT)
+    load_both(m, o, [(topic([b"*", b"#"]), "q%02d" % rng.randrange(40), rng.random() < 0.5) for _ in range(600)])
+    keys = [topic([b"zzzzzzzzzzzz"]) for _ in range(3000)]
+    r = assert_same_routing(m, o, *pack(keys))
+    assert len(r.queue_ids) > 1000
+    d, od = GpuMatcher(CHQ_DIRECT), po.Oracle(po.DIRECT)   # whole key = one word, up to 255 bytes
+    long_keys = [bytes(rng.choice(b"ab.") for _ in range(rng.choice([0, 1, 7, 8, 9, 15, 16, 17, 64, 200, 255]))) for _ in range(300)]
+    load_both(d, od, [(k, "q%d" % (i % 7), False) for i, k in enumerate(long_keys[:150])])
+    assert_same_routing(d, od, *pack(long_keys + [k + b"x" for k in long_keys[:50] if len(k) < 255]))
+
+
+def test_misaligned_key_blob_on_the_device():
+    """chq_route_device with the key bytes starting at every address modulo 4"""
+    torch = pytest.importorskip("torch")
+    w, m, o = _load_workload(2, 20_000, 20_000, CHQ_MODE_COMPAT, True)
+    blob, off = w.keys(5_000, stream=9)
+    n = len(off) - 1
+    o_off, o_ids, o_dur, o_err = o.route_packed(blob, off, 2)
+    dev = torch.device("cuda:0")
+    d_off = torch.from_numpy(off.view(np.int32).copy()).to(dev)
+    d_offsets = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    d_ids = torch.empty(len(o_ids) + 1, dtype=torch.int32, device=dev)
+    d_dur = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_err = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_tot = torch.zeros(2, dtype=torch.int64, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    for shift in range(4):
+        buf = torch.zeros(len(blob) + 8, dtype=torch.uint8, device=dev)
+        buf[shift:shift + len(blob)] = torch.from_numpy(blob.copy()).to(dev)
+        buf[shift + len(blob):] = ord(".")   # whatever follows the blob must not leak into the last key
+        m.route_device(buf.data_ptr() + shift, d_off.data_ptr(), n, d_offsets.data_ptr(), d_ids.data_ptr(), len(o_ids) + 1,
+                       d_dur.data_ptr(), d_err.data_ptr(), d_tot.data_ptr(), d_tot.data_ptr() + 8, st)
+        torch.cuda.synchronize()
+        assert (int(d_tot[1].item()) & 0xFFFFFFFF) == 0 and int(d_tot[0].item()) == len(o_ids)
+        assert np.array_equal(d_offsets.cpu().numpy().view(np.uint32), o_off), shift
+        assert np.array_equal(d_ids[:len(o_ids)].cpu().numpy().view(np.uint32), o_ids), shift
+
+
+@pytest.mark.parametrize("max_small", [0, 1, 40])
+def test_several_long_lists_without_shared_queues(max_small):
+    """messages whose matched lists are all long and disjoint: merged in place by the multi-way path
+    (list lengths around the 32-id window, up to 8 lists)"""
+    rng = random.Random(31 + max_small)
+    m, o = GpuMatcher(CHQ_TOPIC, CHQ_MODE_SPEC), po.Oracle(po.TOPIC, po.SPEC)
+    m.debug_limits(0, max_small)
+    pats = ["a.#", "a.b.#", "a.*.c", "a.b.c", "*.b.c", "a.b.*", "#", "*.*.c", "a.b.c.#", "x.y", "x.*", "x.#"]
+    sizes = [500, 333, 64, 32, 31, 33, 129, 1, 97, 1000, 999, 65]
+    binds, q = [], 0
+    order = list(range(200000))
+    rng.shuffle(order)   # queue names in random order, so the lists interleave
+    for pat, sz in zip(pats, sizes):
+        for _ in range(sz):
+            binds.append((pat, "q%06d" % order[q], rng.random() < 0.2))
+            q += 1
+    rng.shuffle(binds)
+    load_both(m, o, binds)
+    keys = ["a.b.c", "a.b", "a", "a.z.c", "x.y", "x.z", "x", "q", "a.b.c.d", "z.b.c", "a.b.d"] * 40
+    r = assert_same_routing(m, o, *pack(keys))
+    check_csr_invariants(r, m.n_queues())
+    cnt = np.diff(r.offsets.astype(np.int64))
+    assert int(cnt[0]) == sum(sizes[:9]) and int(cnt[4]) == sizes[9] + sizes[10] + sizes[11] + sizes[6]
