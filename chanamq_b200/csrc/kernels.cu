@@ -546,18 +546,17 @@ struct WriteCtx {  // the few fields of RouteParams it needs, by value (kernel p
   uint32_t* ids;
   uint64_t ids_cap;
 };
-__device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws, uint32_t mm, uint32_t c, uint32_t mt,
-                                           uint64_t o, int lane) {
+// (lo, ll) = this lane's entry of the message's list row (lane j < k: list j), fetched by the caller ahead of time.
+__device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws, uint32_t lo, uint32_t ll, uint32_t c,
+                                              uint32_t mt, uint64_t o, int lane) {
   const int kk = mt & 0xFF, cl = (mt >> 8) & 0xF;
-  const uint2* ml = p.mlist + (size_t)mm * kRouteSlots;
   CHQ_CLK_T0();
   if (cl == 2) {
-    const uint2 s2 = __ldg(ml);
-    const uint64_t so = ((uint64_t)s2.y << 32) | s2.x;
+    const uint64_t so = ((uint64_t)__shfl_sync(kFull, ll, 0) << 32) | __shfl_sync(kFull, lo, 0);
     for (uint32_t i = lane; i < c; i += 32) p.ids[o + i] = p.scratch[so + i];
     CHQ_CLK_ADD(3, 1, c);
   } else if (kk == 1) {
-    const uint32_t* sp = p.qlist + __ldg(ml).x + lane;
+    const uint32_t* sp = p.qlist + __shfl_sync(kFull, lo, 0) + lane;
     uint32_t* dst = p.ids + o + lane;
     uint32_t i = lane;
     for (; i + 96 < c; i += 128, sp += 128, dst += 128) {
@@ -567,8 +566,7 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
     for (; i < c; i += 32, sp += 32, dst += 32) *dst = __ldg(sp);
     CHQ_CLK_ADD(2, 1, c);
   } else {
-    uint32_t lo = 0, ll = 0;
-    if (lane < kk) { const uint2 d = __ldg(ml + lane); lo = d.x; ll = d.y; }
+    if (lane >= kk) lo = ll = 0;
     if (cl == 3) warp_union_long(p.qlist, lo, ll, kk, ws, p.ids, o, lane);
     else warp_union<true>(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, p.ids_cap, lane);
 #ifdef CHQ_CLOCKS
@@ -626,9 +624,19 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RoutePa
         }
         const bool big = (meta & kMetaBig) != 0;
         const bool sel = cnt > 0 && fits && !(meta & kMetaTiny) && (pass == 0 ? big : !big);
-        for (unsigned todo = __ballot_sync(kFull, sel); todo; todo &= todo - 1) {
+        // the list row of the next message is fetched while the current one is written
+        unsigned todo = __ballot_sync(kFull, sel);
+        auto row_of = [&](unsigned td) -> uint2 {
+          if (td == 0 || lane >= kRouteSlots) return make_uint2(0u, 0u);
+          return __ldg(p.mlist + (size_t)(base + __ffs(td) - 1) * kRouteSlots + lane);
+        };
+        uint2 row = row_of(todo);
+        while (todo) {
           const int src = __ffs(todo) - 1;
-          write_message(wc, ws, base + src, __shfl_sync(kFull, cnt, src), __shfl_sync(kFull, meta, src),
+          todo &= todo - 1;
+          const uint2 mine = row;
+          row = row_of(todo);
+          write_message(wc, ws, mine.x, mine.y, __shfl_sync(kFull, cnt, src), __shfl_sync(kFull, meta, src),
                         __shfl_sync(kFull, pos, src), lane);
         }
       }
