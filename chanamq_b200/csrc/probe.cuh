@@ -136,14 +136,20 @@ __device__ __forceinline__ bool shape_hash(const Shape& sh, const KeyCtx& k, uin
   return true;
 }
 
-// eight 16-bit tags against one: bit i of the result = slot i matches; full = no empty slot
+// eight 16-bit tags against one: bit i of the result = slot i matches; full = no empty slot.
+// Slots of a bucket are filled in order at build time and a tag is never 0, so the bucket is full exactly
+// when its last slot is taken.  zero16() flags the zero halfwords of a word (bits 15 and 31), exactly.
+__device__ __forceinline__ uint32_t zero16(uint32_t x) {
+  const uint32_t y = (x & 0x7FFF7FFFu) + 0x7FFF7FFFu;
+  return ~(y | x | 0x7FFF7FFFu);
+}
 __device__ __forceinline__ uint32_t match_tags(const uint4& t, uint32_t tag, bool& full) {
   const uint32_t tt = tag * 0x10001u;
-  const uint32_t c0 = __vcmpeq2(t.x, tt), c1 = __vcmpeq2(t.y, tt), c2 = __vcmpeq2(t.z, tt), c3 = __vcmpeq2(t.w, tt);
-  full = (__vcmpeq2(t.x, 0) | __vcmpeq2(t.y, 0) | __vcmpeq2(t.z, 0) | __vcmpeq2(t.w, 0)) == 0;
+  const uint32_t c0 = zero16(t.x ^ tt), c1 = zero16(t.y ^ tt), c2 = zero16(t.z ^ tt), c3 = zero16(t.w ^ tt);
+  full = (t.w >> 16) != 0;
   if ((c0 | c1 | c2 | c3) == 0) return 0;
-  return (c0 & 1u) | ((c0 >> 15) & 2u) | ((c1 & 1u) << 2) | ((c1 >> 13) & 8u) | ((c2 & 1u) << 4) | ((c2 >> 11) & 32u) |
-         ((c3 & 1u) << 6) | ((c3 >> 9) & 128u);
+  return ((c0 >> 15) & 1u) | ((c0 >> 30) & 2u) | ((c1 >> 13) & 4u) | ((c1 >> 28) & 8u) | ((c2 >> 11) & 16u) |
+         ((c2 >> 26) & 32u) | ((c3 >> 9) & 64u) | ((c3 >> 24) & 128u);
 }
 
 __device__ bool remainder_matches(const TableView& tv, uint32_t rem_off, uint32_t rem_len, const uint32_t* __restrict__ row,

@@ -89,3 +89,43 @@ def queue_names_packed(queue_idx):
         v //= 10
     off = (np.arange(n + 1, dtype=np.uint64) * 8).astype(np.uint32)
     return digits.reshape(-1), off
+
+
+class HeadersWorkload:
+    """Config 3 of SURVEY.md §8(d): headers exchange, 8 fields per message, 8 argument slots per binding
+    (chanamq_b200/workload/gen_headers.cpp)."""
+
+    def __init__(self, seed, n_templates=100_000):
+        L = self.L = _lib()
+        L.chqgen_headers_new.restype = C.c_void_p
+        L.chqgen_headers_new.argtypes = [C.c_uint64, C.c_uint32]
+        L.chqgen_headers_free.argtypes = [C.c_void_p]
+        L.chqgen_headers_max_bytes.restype = C.c_uint32
+        L.chqgen_headers_messages.restype = C.c_uint64
+        L.chqgen_headers_messages.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.chqgen_headers_bindings.restype = C.c_uint64
+        L.chqgen_headers_bindings.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.g = L.chqgen_headers_new(seed, n_templates)
+        self.max_bytes = L.chqgen_headers_max_bytes()
+
+    def __del__(self):
+        if getattr(self, "g", None):
+            self.L.chqgen_headers_free(self.g)
+            self.g = None
+
+    def messages(self, n, stream=0):
+        """-> (blob uint8[], off uint32[n+1]): the messages' headers tables (field-table contents)"""
+        blob = np.empty(n * self.max_bytes + 16, dtype=np.uint8)
+        off = np.empty(n + 1, dtype=np.uint32)
+        used = self.L.chqgen_headers_messages(self.g, stream, n, blob.ctypes.data, off.ctypes.data)
+        return blob[:max(int(used), 1)], off
+
+    def bindings(self, p, n_queues=None):
+        """-> (blob, off uint32[p+1], queue_idx uint32[p], durable uint8[p]): argument tables incl. x-match"""
+        blob = np.empty(p * self.max_bytes + 16, dtype=np.uint8)
+        off = np.empty(p + 1, dtype=np.uint32)
+        q = np.empty(p, dtype=np.uint32)
+        d = np.empty(p, dtype=np.uint8)
+        used = self.L.chqgen_headers_bindings(self.g, p, n_queues or p, blob.ctypes.data, off.ctypes.data, q.ctypes.data,
+                                              d.ctypes.data)
+        return blob[:max(int(used), 1)], off, q, d
