@@ -395,7 +395,8 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
     }
   }
   // classify: 0 = count known, 1 = needs the de-duplicating merge to count, 2 = slow path (result parked in
-  // scratch), 3 = count known, several long lists (k_write merges them with warp_union_long)
+  // scratch), 3 = count known, several long lists (k_write merges them with warp_union_long), 4 = more lists
+  // than slots but few ids, lists described in global memory (k_write: warp_gather_small)
   int cls = 0;
   const bool dedup = (flags & kShared) != 0;
   // tiny: the whole result fits the 16-input sorting network of one thread (merge.cuh)
@@ -404,6 +405,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   auto my_len = [&](uint32_t j) { return sm.llen[j][tid]; };
   if (tiny) cnt = (k == 1 || !dedup) ? ub : tiny_union(tv.qlist, k, my_off, my_len, nullptr);
   else if (overflow) cls = 2;
+  else if (p.desc_k && k > p.max_slots && k <= (uint32_t)kRouteSmall && ub <= (uint32_t)kRouteSmall) { cls = 4; cnt = ub; }
   else if (k <= 1) cnt = ub;
   else if (k > p.max_slots || (dedup && ub - mxlen > p.max_small)) cls = 2;
   else if (ub - mxlen > p.max_small) { cls = 3; cnt = ub; }
@@ -432,6 +434,13 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
     }
     if (lane == src) { cnt = c; flags = fl; scr = so; }
   }
+  for (unsigned todo = __ballot_sync(kFull, cls == 4 && dedup); todo; todo &= todo - 1) {
+    const int src = __ffs(todo) - 1;
+    const uint32_t mm = blockIdx.x * kRouteThreads + warp * 32 + src;
+    const uint32_t c = warp_gather_small<false>(tv.qlist, p.desc_lists + __ldg(p.desc_start + mm), __shfl_sync(kFull, k, src),
+                                                true, sm.ws[warp], nullptr, 0, lane);
+    if (lane == src) cnt = c;
+  }
   for (unsigned todo = __ballot_sync(kFull, cls == 1); todo; todo &= todo - 1) {
     const int src = __ffs(todo) - 1;
     const int kk = __shfl_sync(kFull, k, src);
@@ -448,6 +457,8 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   uint2* lists = p.mlist + (size_t)m * kRouteSlots;
   if (cls == 2) {
     lists[0] = make_uint2((uint32_t)scr, (uint32_t)(scr >> 32));
+  } else if (cls == 4) {
+    lists[0] = make_uint2(__ldg(p.desc_start + m), 0u);  // where its descriptors start in the arena
   } else if (cnt > 0) {
     for (uint32_t j = 0; j < k; ++j) lists[j] = make_uint2(sm.loff[j][tid], sm.llen[j][tid]);
   }
@@ -540,6 +551,7 @@ __global__ void __launch_bounds__(kScanThreads) k_offsets(RouteParams p) {
 // k_write has ONE call site for it (both passes share the loop) so that the kernel stays inside the
 // instruction cache.
 struct WriteCtx {  // the few fields of RouteParams it needs, by value (kernel parameters have no address)
+  const uint2* desc_lists;
   const uint32_t* qlist;
   const uint2* mlist;
   const uint32_t* scratch;
@@ -554,6 +566,9 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
   if (cl == 2) {
     const uint64_t so = ((uint64_t)__shfl_sync(kFull, ll, 0) << 32) | __shfl_sync(kFull, lo, 0);
     for (uint32_t i = lane; i < c; i += 32) p.ids[o + i] = p.scratch[so + i];
+    CHQ_CLK_ADD(3, 1, c);
+  } else if (cl == 4) {
+    warp_gather_small<true>(p.qlist, p.desc_lists + __shfl_sync(kFull, lo, 0), kk, (mt & kMetaDedup) != 0, ws, p.ids, o, lane);
     CHQ_CLK_ADD(3, 1, c);
   } else if (kk == 1) {
     const uint32_t* sp = p.qlist + __shfl_sync(kFull, lo, 0) + lane;
@@ -584,7 +599,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RoutePa
   WarpScratch& ws = ws_all[warp];
   const uint32_t n_chunks = (p.n + 31) / 32;
   if (*p.total > 0xFFFFFFFFull || (p.debug & 1u)) return;  // offsets saturated: the launch reports CHQ_E_OVERFLOW
-  const WriteCtx wc{tv.qlist, p.mlist, p.scratch, p.ids, p.ids_cap};
+  const WriteCtx wc{p.desc_lists, tv.qlist, p.mlist, p.scratch, p.ids, p.ids_cap};
   // Two passes over the batch, 32 consecutive messages per sub-chunk.  Pass 0 sweeps the meta words (four
   // sub-chunks per grab) and does only the few messages with long results, so that the longest jobs start
   // first instead of being met by chance near the end of the kernel; pass 1 does everything else.

@@ -478,5 +478,83 @@ __device__ void warp_union_long(const uint32_t* __restrict__ qlist, uint32_t my_
   __syncwarp();
 }
 
+// Union of k <= 32 lists holding at most 32 ids together, given as (offset, length) descriptors in global
+// memory (the headers exchange: a message typically meets a dozen one-queue lists).  One id per lane,
+// shuffle bitonic sort, neighbours compared to drop duplicates.  Returns the size of the union; with WRITE
+// it goes to out[pos ...).
+template <bool WRITE>
+__device__ uint32_t warp_gather32(const uint32_t* __restrict__ qlist, const uint2* __restrict__ desc, uint32_t k, bool dedup,
+                                  uint32_t* __restrict__ out, uint64_t pos, int lane) {
+  uint2 d = make_uint2(0u, 0u);
+  if ((uint32_t)lane < k) d = __ldg(desc + lane);
+  uint32_t incl = d.y;
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) {
+    const uint32_t v = __shfl_up_sync(kFull, incl, s);
+    if (lane >= s) incl += v;
+  }
+  const uint32_t total = __shfl_sync(kFull, incl, 31);
+  // lane i takes the i-th id overall: the list whose [start, start + len) holds i
+  uint32_t id = kNone;
+  for (uint32_t j = 0; j < k; ++j) {
+    const uint32_t o = __shfl_sync(kFull, d.x, j), l = __shfl_sync(kFull, d.y, j);
+    const uint32_t st = __shfl_sync(kFull, incl, j) - l;
+    if ((uint32_t)lane >= st && (uint32_t)lane < st + l) id = __ldg(qlist + o + (lane - st));
+  }
+#pragma unroll
+  for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+    for (int dd = size >> 1; dd; dd >>= 1) {
+      const uint32_t other = __shfl_xor_sync(kFull, id, dd);
+      const bool up = (lane & size) == 0, lower = (lane & dd) == 0;
+      id = (lower == up) ? min(id, other) : max(id, other);
+    }
+  }
+  const uint32_t prev = __shfl_up_sync(kFull, id, 1);
+  const bool keep = (uint32_t)lane < total && !(dedup && lane > 0 && id == prev);
+  const unsigned km = __ballot_sync(kFull, keep);
+  if (WRITE && keep) out[pos + __popc(km & ((1u << lane) - 1))] = id;
+  return __popc(km);
+}
+
+// The same for up to kRouteSmall ids in any number of lists: every lane copies whole lists (they are short)
+// into shared memory, then a bitonic sort there.
+template <bool WRITE>
+__device__ uint32_t warp_gather_small(const uint32_t* __restrict__ qlist, const uint2* __restrict__ desc, uint32_t k,
+                                      bool dedup, WarpScratch& ws, uint32_t* __restrict__ out, uint64_t pos, int lane) {
+  if (k <= 32) {
+    uint32_t sum = (uint32_t)lane < k ? __ldg(desc + lane).y : 0u;
+#pragma unroll
+    for (int s = 16; s; s >>= 1) sum += __shfl_xor_sync(kFull, sum, s);
+    if (sum <= 32) return warp_gather32<WRITE>(qlist, desc, k, dedup, out, pos, lane);
+  }
+  uint32_t wpos = 0;
+  for (uint32_t base = 0; base < k; base += 32) {
+    uint2 d = make_uint2(0u, 0u);
+    if (base + lane < k) d = __ldg(desc + base + lane);
+    uint32_t incl = d.y;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const uint32_t v = __shfl_up_sync(kFull, incl, s);
+      if (lane >= s) incl += v;
+    }
+    const uint32_t st = wpos + incl - d.y;
+    for (uint32_t i = 0; i < d.y && st + i < (uint32_t)kRouteSmall; ++i) ws.a[st + i] = __ldg(qlist + d.x + i);
+    wpos += __shfl_sync(kFull, incl, 31);
+  }
+  const uint32_t total = min(wpos, (uint32_t)kRouteSmall);
+  uint32_t np = 32;
+  while (np < total) np <<= 1;
+  for (uint32_t i = total + lane; i < np; i += 32) ws.a[i] = kNone;
+  __syncwarp();
+  warp_bitonic_sort(ws.a, np, lane);
+  const uint32_t cnt = dedup ? warp_unique(ws.a, total, lane) : total;
+  __syncwarp();
+  if (WRITE)
+    for (uint32_t i = lane; i < cnt; i += 32) out[pos + i] = ws.a[i];
+  __syncwarp();
+  return cnt;
+}
+
 }  // namespace
 }  // namespace chq
