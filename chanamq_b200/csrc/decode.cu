@@ -18,6 +18,7 @@
 #include <stdint.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 
 #include "kernels.h"
@@ -273,6 +274,226 @@ __global__ void k_frame_scan(const uint8_t* __restrict__ b, const uint64_t* __re
   seg_err_off[s] = err ? eoff : 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Chunked scan: a long segment walked by many threads.
+//
+// The scan loop above visits a chain of IDLE positions (starts of METHOD frames or of heartbeats met between
+// commands), each found from the one before.  Here a segment is cut into chunks of `chunk` bytes; the thread
+// of chunk j > 0 GUESSES the first idle position at or after its chunk start (the first byte position from
+// which a whole command parses and is followed by another plausible command), walks the chain from there to
+// the end of its chunk, and notes where it came out.  k_chunk_validate then checks the chain exactly: chunk 0
+// starts at the segment start; chunk j's walk stands only if it started where chunk j-1 really came out,
+// otherwise that chunk is walked again from the true position (bodies full of frame look-alikes, frames longer
+// than a chunk: slower, never wrong).  The result is the sequential scan's, bit for bit.
+// ------------------------------------------------------------------------------------------------
+constexpr uint64_t kNoPos = ~0ull;
+struct ChunkRes {      // what one walk found
+  uint64_t entry;      // idle position it started from (kNoPos: no guess found)
+  uint64_t exit;       // first idle position at or after the chunk end, or where it stopped
+  uint64_t eoff;       // error offset
+  uint32_t count;      // commands started inside the chunk
+  int32_t err;
+  uint32_t stopped;    // 1: the chain ends here (incomplete tail or error)
+  uint32_t pad;
+};
+
+// where chunk v keeps its command offsets: a command takes at least 12 wire bytes
+__device__ __host__ inline uint64_t chunk_list_base(uint64_t chunk_start, uint32_t v) { return chunk_start / 12 + v; }
+
+// Walks the idle positions from `pos` while they are below `limit`.
+__device__ void walk_chunk(const uint8_t* __restrict__ b, uint64_t pos, uint64_t limit, uint64_t seg_end, uint32_t seg,
+                           uint32_t* __restrict__ list, ChunkRes& r) {
+  r.entry = pos; r.count = 0; r.err = 0; r.eoff = 0; r.stopped = 0; r.pad = 0;
+  while (pos < limit) {
+    FrameHdr f;
+    const FrameStatus fs = read_frame(b, pos, seg_end, f);
+    if (fs == kFrameIncomplete) { r.stopped = 1; break; }
+    if (fs == kFrameNegative) { r.err = kErrThrown; r.eoff = pos; r.stopped = 1; break; }
+    if (fs == kFrameBadEnd) { r.err = kErrFrame; r.eoff = pos; r.stopped = 1; break; }
+    if (f.type == 8) { pos += 8 + (uint64_t)f.size; continue; }
+    uint64_t next = pos;
+    const CmdStatus cs = parse_command(b, pos, seg_end, seg, nullptr, &next, &r.err, &r.eoff);
+    if (cs != kCmdDone) { if (cs == kCmdIncomplete) { r.err = 0; r.eoff = 0; } r.stopped = 1; break; }
+    list[r.count++] = (uint32_t)pos;
+    pos = next;
+  }
+  r.exit = pos;
+}
+
+// Could an idle position be at p?  0 no; else the position the chain would go to next (p itself if the command
+// at p is still incomplete at the segment end).
+__device__ uint64_t plausible_idle(const uint8_t* __restrict__ b, uint64_t p, uint64_t seg_end, uint32_t seg) {
+  FrameHdr f;
+  if (read_frame(b, p, seg_end, f) != kFrameOk) return 0;
+  if (f.type == 8) return (f.size == 0 && f.channel == 0) ? p + 8 : 0;
+  if (f.type != 1) return 0;
+  uint64_t next = p, eoff;
+  int32_t err;
+  const CmdStatus cs = parse_command(b, p, seg_end, seg, nullptr, &next, &err, &eoff);
+  if (cs == kCmdError) return 0;
+  return cs == kCmdDone ? next : p;
+}
+
+// First position in [from, to) that looks like an idle position and is followed by another one.
+__device__ uint64_t guess_idle(const uint8_t* __restrict__ b, uint64_t from, uint64_t to, uint64_t seg_end, uint32_t seg) {
+  auto test = [&](uint64_t p) -> bool {
+    const uint64_t q = plausible_idle(b, p, seg_end, seg);
+    if (q == 0) return false;
+    if (q == p || q + 7 > seg_end) return true;           // runs into the end of the segment
+    return plausible_idle(b, q, seg_end, seg) != 0;
+  };
+  uint64_t p = from;
+  // bytes up to the next 16-byte boundary one by one, then sixteen at a time: only a 0x01 (METHOD) or a 0x08
+  // (heartbeat) byte can start an idle position
+  for (; p < to && ((reinterpret_cast<uintptr_t>(b) + p) & 15u); ++p) {
+    const uint8_t c = __ldg(b + p);
+    if ((c == 1 || c == 8) && test(p)) return p;
+  }
+  for (; p + 16 <= to; p += 16) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(b + p));
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t any = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t a = w[i] ^ 0x01010101u, c = w[i] ^ 0x08080808u;
+      any |= ((a - 0x01010101u) & ~a & 0x80808080u) | ((c - 0x01010101u) & ~c & 0x80808080u);
+    }
+    if (!any) continue;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t c = (w[i] >> (8 * j)) & 0xFFu;
+        if ((c == 1 || c == 8) && test(p + 4 * i + j)) return p + 4 * i + j;
+      }
+  }
+  for (; p < to; ++p) {
+    const uint8_t c = __ldg(b + p);
+    if ((c == 1 || c == 8) && test(p)) return p;
+  }
+  return kNoPos;
+}
+
+// chunks per segment -> chunk_base[n_seg + 1] (one block)
+__global__ void k_chunk_plan(const uint64_t* __restrict__ seg_off, uint32_t n_seg, uint64_t chunk, uint32_t* __restrict__ chunk_base) {
+  __shared__ uint32_t carry;
+  __shared__ uint32_t warp_tot[32];
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < n_seg; base += blockDim.x) {
+    const uint32_t i = base + threadIdx.x;
+    uint32_t v = 0;
+    if (i < n_seg) {
+      const uint64_t len = seg_off[i + 1] - seg_off[i];
+      v = (uint32_t)max((len + chunk - 1) / chunk, (uint64_t)1);
+    }
+    uint32_t incl = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if ((threadIdx.x & 31) >= d) incl += t;
+    }
+    if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    uint32_t wbase = 0;
+    for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) wbase += warp_tot[w];
+    if (i < n_seg) chunk_base[i] = carry + wbase + incl - v;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry += wbase + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) chunk_base[n_seg] = carry;
+}
+
+// one thread per chunk: guess the entry, walk
+__global__ void k_chunk_walk(const uint8_t* __restrict__ b, const uint64_t* __restrict__ seg_off, uint32_t n_seg, uint64_t chunk,
+                             const uint32_t* __restrict__ chunk_base, uint32_t max_chunks, uint32_t* __restrict__ cmd_off,
+                             ChunkRes* __restrict__ res, uint32_t* __restrict__ chunk_seg, uint64_t* __restrict__ chunk_start,
+                             uint64_t* __restrict__ chunk_count) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= max_chunks) return;
+  if (v >= chunk_base[n_seg]) { chunk_seg[v] = n_seg - 1; chunk_start[v] = 0; chunk_count[v] = 0; return; }
+  uint32_t lo = 0, hi = n_seg;  // last segment whose first chunk <= v
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (chunk_base[mid] <= v) lo = mid; else hi = mid;
+  }
+  const uint32_t s = lo, j = v - chunk_base[s];
+  const uint64_t begin = seg_off[s], end = seg_off[s + 1];
+  const uint64_t cs = begin + (uint64_t)j * chunk, ce = min(cs + chunk, end);
+  chunk_seg[v] = s;
+  chunk_start[v] = cs;
+  ChunkRes r;
+  const uint64_t entry = j == 0 ? begin : guess_idle(b, cs, ce, end, s);
+  if (entry == kNoPos) { r.entry = kNoPos; r.exit = kNoPos; r.eoff = 0; r.count = 0; r.err = 0; r.stopped = 0; r.pad = 0; }
+  else walk_chunk(b, entry, ce, end, s, cmd_off + chunk_list_base(cs, v), r);
+  res[v] = r;
+}
+
+// one warp per segment: the chain of chunk walks, checked 32 links at a time
+__global__ void k_chunk_validate(const uint8_t* __restrict__ b, const uint64_t* __restrict__ seg_off, uint32_t n_seg, uint64_t chunk,
+                                 const uint32_t* __restrict__ chunk_base, uint32_t* __restrict__ cmd_off, ChunkRes* __restrict__ res,
+                                 uint64_t* __restrict__ chunk_count, uint64_t* __restrict__ seg_consumed,
+                                 int32_t* __restrict__ seg_err, uint64_t* __restrict__ seg_err_off) {
+  const uint32_t s = blockIdx.x;
+  const int lane = threadIdx.x;
+  const uint32_t c_lo = chunk_base[s], c_hi = chunk_base[s + 1];
+  const uint64_t begin = seg_off[s], end = seg_off[s + 1];
+  uint64_t entry = begin, eoff = 0;
+  int32_t err = 0;
+  bool stopped = false;
+  uint32_t c = c_lo;
+  while (c < c_hi) {
+    if (stopped) {  // nothing after the point where the chain ended counts
+      for (uint32_t t = c + lane; t < c_hi; t += 32) chunk_count[t] = 0;
+      break;
+    }
+    const uint32_t t = c + lane;
+    const bool have = t < c_hi;
+    ChunkRes r;
+    r.entry = kNoPos; r.exit = kNoPos; r.stopped = 0; r.count = 0; r.err = 0; r.eoff = 0;
+    if (have) r = res[t];
+    uint64_t prev_exit = __shfl_up_sync(0xFFFFFFFFu, r.exit, 1);
+    uint32_t prev_stop = __shfl_up_sync(0xFFFFFFFFu, r.stopped, 1);
+    if (lane == 0) { prev_exit = entry; prev_stop = 0; }
+    const bool ok = have && r.entry != kNoPos && r.entry == prev_exit && !prev_stop;
+    const unsigned good = __ballot_sync(0xFFFFFFFFu, ok);
+    const int f = (~good) ? __ffs(~good) - 1 : 32;  // the links before lane f hold
+    if (lane < f) chunk_count[t] = r.count;
+    if (f > 0) {
+      entry = __shfl_sync(0xFFFFFFFFu, r.exit, f - 1);
+      if (__shfl_sync(0xFFFFFFFFu, r.stopped, f - 1)) {
+        stopped = true;
+        err = __shfl_sync(0xFFFFFFFFu, r.err, f - 1);
+        eoff = __shfl_sync(0xFFFFFFFFu, r.eoff, f - 1);
+      }
+    }
+    c += f;
+    if (stopped || c >= c_hi || f == 32) continue;
+    // chunk c was walked from the wrong place (or not at all): do it again from where the chain really is
+    const uint64_t cs = begin + (uint64_t)(c - c_lo) * chunk, ce = min(cs + chunk, end);
+    ChunkRes fix;
+    fix.exit = entry; fix.stopped = 0; fix.err = 0; fix.eoff = 0; fix.count = 0;
+    if (lane == 0) {
+      if (entry < ce) {
+        walk_chunk(b, entry, ce, end, s, cmd_off + chunk_list_base(cs, c), fix);
+        res[c] = fix;
+      }  // else: a frame spans the whole chunk, no idle position inside it
+      chunk_count[c] = fix.count;
+    }
+    entry = __shfl_sync(0xFFFFFFFFu, fix.exit, 0);
+    if (__shfl_sync(0xFFFFFFFFu, fix.stopped, 0)) {
+      stopped = true;
+      err = __shfl_sync(0xFFFFFFFFu, fix.err, 0);
+      eoff = __shfl_sync(0xFFFFFFFFu, fix.eoff, 0);
+    }
+    ++c;
+  }
+  if (lane == 0) {
+    seg_consumed[s] = entry - begin;
+    seg_err[s] = err;
+    seg_err_off[s] = err ? eoff : 0;
+  }
+}
+
 // exclusive prefix sum of the per-segment command counts (n_seg is small: one block)
 __global__ void k_seg_scan(const uint64_t* __restrict__ seg_count, uint32_t n_seg, uint64_t* __restrict__ rec_base,
                            uint64_t* __restrict__ n_recs, uint64_t recs_cap, int32_t* __restrict__ status) {
@@ -304,20 +525,23 @@ __global__ void k_seg_scan(const uint64_t* __restrict__ seg_count, uint32_t n_se
   }
 }
 
-// K5: one thread per command (grid-stride: the count lives on the device).
+// K5: one thread per command (grid-stride: the count lives on the device).  The command lists are per
+// segment (chunk_seg == null) or per chunk of a segment (n_seg = number of chunks, chunk_seg / chunk_start
+// say which segment a chunk belongs to and where it starts).
 __global__ void k_publish_decode(const uint8_t* __restrict__ b, const uint64_t* __restrict__ seg_off, uint32_t n_seg,
                                  const uint32_t* __restrict__ cmd_off, const uint64_t* __restrict__ rec_base,
-                                 chq_publish_rec* __restrict__ recs, uint64_t recs_cap) {
+                                 chq_publish_rec* __restrict__ recs, uint64_t recs_cap, const uint32_t* __restrict__ chunk_seg,
+                                 const uint64_t* __restrict__ chunk_start) {
   const uint64_t total = min(rec_base[n_seg], recs_cap);
   for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
-    uint32_t lo = 0, hi = n_seg;  // last segment whose base <= i
+    uint32_t lo = 0, hi = n_seg;  // last list whose base <= i
     while (hi - lo > 1) {
       const uint32_t mid = (lo + hi) >> 1;
       if (rec_base[mid] <= i) lo = mid; else hi = mid;
     }
-    const uint32_t s = lo;
-    const uint64_t begin = seg_off[s];
-    const uint64_t pos = cmd_off[seg_list_base(begin, s) + (i - rec_base[s])];  // the batch is < 4 GiB
+    const uint32_t s = chunk_seg ? chunk_seg[lo] : lo;
+    const uint64_t base = chunk_seg ? chunk_list_base(chunk_start[lo], lo) : seg_list_base(seg_off[s], s);
+    const uint64_t pos = cmd_off[base + (i - rec_base[lo])];  // the batch is < 4 GiB
     uint64_t next, eoff;
     int32_t err;
     chq_publish_rec rec;
@@ -357,6 +581,10 @@ int dfail(int code, const std::string& m) { g_dec_err = m; return code; }
 
 struct DecodeScratch {  // per device; grown on demand
   uint32_t* cmd_off = nullptr; size_t cmd_cap = 0;      // command offsets found by the scan
+  uint32_t* chunk_base = nullptr; size_t cbase_cap = 0; // chunked scan: first chunk of every segment
+  ChunkRes* chunk_res = nullptr; size_t cres_cap = 0;
+  uint32_t* chunk_seg = nullptr; size_t cseg_cap = 0;
+  uint64_t* chunk_start = nullptr; size_t cstart_cap = 0;
   uint64_t* seg_count = nullptr; size_t count_cap = 0;
   uint64_t* rec_base = nullptr; size_t base_cap = 0;
   // host-buffer entry point
@@ -394,21 +622,53 @@ int32_t chq_decode_device(const uint8_t* d_bytes, uint64_t len, const uint64_t* 
   DecodeScratch& sc = g_scratch[dev & 63];
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
-  if ((rc = grow(&sc.cmd_off, &sc.cmd_cap, (size_t)(len / 12 + n_seg + 1)))) return rc;
-  if ((rc = grow(&sc.seg_count, &sc.count_cap, (size_t)n_seg + 1))) return rc;
-  if ((rc = grow(&sc.rec_base, &sc.base_cap, (size_t)n_seg + 1))) return rc;
+  // Segments are cut into chunks of this many bytes, one scanning thread each (CHQ_DECODE_CHUNK overrides the
+  // size; 0 = the plain one-thread-per-segment scan).
+  const uint64_t chunk = [] {
+    const char* e = getenv("CHQ_DECODE_CHUNK");
+    const long long v = e ? atoll(e) : (256ll << 10);
+    return (uint64_t)(v <= 0 ? 0 : (v < 64 ? 64 : v));
+  }();
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (n_seg == 0) {
     DCU(cudaMemsetAsync(d_n_recs, 0, sizeof(uint64_t), st));
     DCU(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
     return CHQ_OK;
   }
-  k_frame_scan<<<(n_seg + 31) / 32, 32, 0, st>>>(d_bytes, d_seg_offsets, n_seg, sc.cmd_off, sc.seg_count, d_seg_consumed,
-                                                  d_seg_err, d_seg_err_off);
-  k_seg_scan<<<1, 1024, 0, st>>>(sc.seg_count, n_seg, sc.rec_base, d_n_recs, recs_cap, d_status);
-  int sms = 148;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  k_publish_decode<<<sms * 8, 256, 0, st>>>(d_bytes, d_seg_offsets, n_seg, sc.cmd_off, sc.rec_base, d_recs, recs_cap);
-  chq::note_launches(3);
+  if (chunk == 0) {
+    if ((rc = grow(&sc.cmd_off, &sc.cmd_cap, (size_t)(len / 12 + n_seg + 1)))) return rc;
+    if ((rc = grow(&sc.seg_count, &sc.count_cap, (size_t)n_seg + 1))) return rc;
+    if ((rc = grow(&sc.rec_base, &sc.base_cap, (size_t)n_seg + 1))) return rc;
+    k_frame_scan<<<(n_seg + 31) / 32, 32, 0, st>>>(d_bytes, d_seg_offsets, n_seg, sc.cmd_off, sc.seg_count, d_seg_consumed,
+                                                    d_seg_err, d_seg_err_off);
+    k_seg_scan<<<1, 1024, 0, st>>>(sc.seg_count, n_seg, sc.rec_base, d_n_recs, recs_cap, d_status);
+    k_publish_decode<<<sms * 8, 256, 0, st>>>(d_bytes, d_seg_offsets, n_seg, sc.cmd_off, sc.rec_base, d_recs, recs_cap, nullptr,
+                                              nullptr);
+    chq::note_launches(3);
+    DCU(cudaGetLastError());
+    return CHQ_OK;
+  }
+  // the segment boundaries live on the device: size everything for the most chunks they can make
+  const uint64_t max_chunks64 = len / chunk + n_seg;
+  if (max_chunks64 >= (1ull << 31)) return dfail(CHQ_E_ARG, "chq_decode_device: too many chunks (raise CHQ_DECODE_CHUNK)");
+  const uint32_t max_chunks = (uint32_t)max_chunks64;
+  if ((rc = grow(&sc.cmd_off, &sc.cmd_cap, (size_t)(len / 12 + max_chunks + 2)))) return rc;
+  if ((rc = grow(&sc.seg_count, &sc.count_cap, (size_t)max_chunks + 1))) return rc;
+  if ((rc = grow(&sc.rec_base, &sc.base_cap, (size_t)max_chunks + 1))) return rc;
+  if ((rc = grow(&sc.chunk_base, &sc.cbase_cap, (size_t)n_seg + 1))) return rc;
+  if ((rc = grow(&sc.chunk_res, &sc.cres_cap, (size_t)max_chunks))) return rc;
+  if ((rc = grow(&sc.chunk_seg, &sc.cseg_cap, (size_t)max_chunks))) return rc;
+  if ((rc = grow(&sc.chunk_start, &sc.cstart_cap, (size_t)max_chunks))) return rc;
+  k_chunk_plan<<<1, 1024, 0, st>>>(d_seg_offsets, n_seg, chunk, sc.chunk_base);
+  k_chunk_walk<<<(max_chunks + 63) / 64, 64, 0, st>>>(d_bytes, d_seg_offsets, n_seg, chunk, sc.chunk_base, max_chunks, sc.cmd_off,
+                                                      sc.chunk_res, sc.chunk_seg, sc.chunk_start, sc.seg_count);
+  k_chunk_validate<<<n_seg, 32, 0, st>>>(d_bytes, d_seg_offsets, n_seg, chunk, sc.chunk_base, sc.cmd_off, sc.chunk_res, sc.seg_count,
+                                         d_seg_consumed, d_seg_err, d_seg_err_off);
+  k_seg_scan<<<1, 1024, 0, st>>>(sc.seg_count, max_chunks, sc.rec_base, d_n_recs, recs_cap, d_status);
+  k_publish_decode<<<sms * 8, 256, 0, st>>>(d_bytes, d_seg_offsets, max_chunks, sc.cmd_off, sc.rec_base, d_recs, recs_cap,
+                                            sc.chunk_seg, sc.chunk_start);
+  chq::note_launches(5);
   DCU(cudaGetLastError());
   return CHQ_OK;
 }

@@ -124,3 +124,51 @@ def test_decode_then_route_on_device():
     assert np.array_equal(d_offsets.cpu().numpy().view(np.uint32), o_off)
     assert np.array_equal(d_ids[: len(o_ids)].cpu().numpy().view(np.uint32), o_ids)
     assert np.array_equal(d_dur.cpu().numpy(), o_dur) and len(o_ids) > 0
+
+
+@pytest.mark.parametrize("chunk", [64, 300, 4096, 0])
+def test_chunked_scan_of_long_segments_is_exact(chunk, monkeypatch):
+    """one segment walked by many threads (CHQ_DECODE_CHUNK bytes each; 0 = the one-thread scan): bodies that
+    contain whole AMQP messages, heartbeats and frame look-alikes (wrong guesses), frames longer than a chunk
+    (chunks without any command start), fragmented bodies, errors and ragged tails"""
+    monkeypatch.setenv("CHQ_DECODE_CHUNK", str(chunk))
+    rng = random.Random(900 + chunk)
+    inner = ab.message("ex", "in.ner.key", b"x" * 40, delivery_mode=2) + ab.heartbeat()
+
+    def body(n):
+        kind = rng.randrange(5)
+        if kind == 0:
+            return bytes(rng.randrange(256) for _ in range(n))
+        if kind == 1:   # a message inside the body, repeated: every guess inside it is wrong
+            return (inner * (n // len(inner) + 1))[:n]
+        if kind == 2:   # bytes that start frames but do not end them
+            return (b"\x01\x00\x01\x00\x00\x00\x05" * (n // 7 + 1))[:n]
+        if kind == 3:
+            return (ab.heartbeat() * (n // 8 + 1))[:n]
+        return b"\xce" * n
+
+    def stream(n_msgs):
+        out = []
+        for i in range(n_msgs):
+            n = rng.choice([0, 1, 7, 50, 300, 1000, 5000])
+            props = {}
+            if rng.random() < 0.3:
+                props = dict(delivery_mode=rng.choice([1, 2]), expiration=str(rng.randrange(10**6)),
+                             headers=[("h", "S", b"v" * rng.randrange(30)), ("n", "I", i)])
+            out.append(ab.message("ex", "k%d.w" % i, body(n), frame_max=rng.choice([None, 64, 1024]), **props))
+            if rng.random() < 0.1:
+                out.append(ab.heartbeat())
+            if rng.random() < 0.05:
+                out.append(ab.other_method(60, 80, b"\x00" * 9))
+        return b"".join(out)
+
+    segs = [stream(rng.choice([1, 30, 120])) for _ in range(6)]
+    segs.append(segs[0][: len(segs[0]) // 2])                    # ragged tail
+    segs.append(b"")                                              # empty segment
+    broken = bytearray(stream(60))
+    broken[len(broken) * 2 // 3] ^= 0x55                          # an error somewhere in the last third
+    segs.append(bytes(broken))
+    seg = np.cumsum([0] + [len(x) for x in segs])
+    got = same(b"".join(segs), seg, "chunk %d" % chunk)
+    assert len(got.recs) > 300
+    same(segs[1] + segs[2] + segs[3], [0, len(segs[1]) + len(segs[2]) + len(segs[3])], "one long segment")
