@@ -214,6 +214,31 @@ int32_t chq_route_keys_device(chq_table* t, const uint8_t* d_bytes, const uint32
                               uint32_t n, uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap,
                               uint8_t* d_any_durable, uint8_t* d_err, uint64_t* d_total, int32_t* d_status, void* stream);
 
+/* ---- the step after the match: per-queue message lists and per-message flags ----
+ * Replaces the tail of ExchangeEntity.publish (chana-mq-server/.../entity/ExchangeEntity.scala:300-307): the
+ * reference appends Msg(msgId, ...) to queueToMsgs(q) for every matched queue, message by message, so each
+ * queue's vector is in publish order.  Here the CSR (d_offsets, d_queue_ids) of a routed batch of n messages is
+ * transposed on the device into d_q_offsets[n_queues + 1] / d_q_msgs[total]: queue q receives the messages
+ * d_q_msgs[d_q_offsets[q] .. d_q_offsets[q + 1]) — indices into the batch, ascending = publish order.
+ * n_queues = chq_n_queues of the table that routed the batch.  Asynchronous on `stream`; *d_status = CHQ_OK,
+ * CHQ_E_OVERFLOW (more ids than q_cap; nothing is written past it) or CHQ_E_ARG (an id >= n_queues). */
+int32_t chq_fanout_device(const uint32_t* d_offsets, const uint32_t* d_queue_ids, uint32_t n, uint32_t n_queues,
+                          uint32_t* d_q_offsets, uint32_t* d_q_msgs, uint64_t q_cap, int32_t* d_status, void* stream);
+/* Per-message results of the publish loop: d_refer_count[i] = number of queues (MessageEntity.Refer count,
+ * ExchangeEntity.scala:303) and d_out_flags[i] = CHQ_FAN_* bits:
+ *   PERSISTENT       exchange durable && message persistent && any matched subscriber durable (ExchangeEntity.scala:302)
+ *   NON_ROUTED       mandatory && no queue                                                      (ExchangeEntity.scala:319-323)
+ *   NON_DELIVERABLE  immediate && no matched queue has a consumer                               (ExchangeEntity.scala:324-330)
+ * d_pub_flags[i] = CHQ_PUB_MANDATORY | CHQ_PUB_IMMEDIATE | CHQ_PUB_PERSIST (the low bits of chq_publish_rec.flags;
+ * NULL = none set); d_queue_has_consumer = one byte per queue id (NULL = no queue has a consumer: the broker keeps
+ * that knowledge in its QueueEntity actors and uploads it when it changes). */
+enum { CHQ_FAN_PERSISTENT = 1, CHQ_FAN_NON_ROUTED = 2, CHQ_FAN_NON_DELIVERABLE = 4 };
+int32_t chq_publish_flags_device(const uint32_t* d_offsets, const uint32_t* d_queue_ids, const uint8_t* d_any_durable,
+                                 const uint8_t* d_pub_flags, uint32_t n, int32_t exchange_durable,
+                                 const uint8_t* d_queue_has_consumer, uint32_t n_queues, uint32_t* d_refer_count,
+                                 uint8_t* d_out_flags, void* stream);
+const char* chq_fanout_last_error(void);
+
 /* pinned host memory for callers that want zero-copy staging (JNA: new Pointer(addr)) */
 int32_t chq_host_alloc(void** p, uint64_t bytes);
 int32_t chq_host_free(void* p);

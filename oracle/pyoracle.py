@@ -241,3 +241,35 @@ class Oracle:
         o, ids, _, err = self.route_packed(blob, off, threads)
         names = self.queue_names()
         return [None if err[i] else [names[j] for j in ids[o[i]:o[i + 1]]] for i in range(len(keys))]
+
+
+# ---- the step after the match (test infrastructure; chana-mq-server/.../entity/ExchangeEntity.scala:300-307, 319-330) ----
+def fanout_transpose(offsets, queue_ids, n_queues):
+    """CSR message -> queue ids  =>  (q_offsets[n_queues + 1], q_msgs[total]): every queue's messages in publish order,
+    which is what `queues foreach { q => queueToMsgs += (q -> (queueToMsgs(q) :+ Msg(...))) }` builds message by message"""
+    off = np.asarray(offsets, dtype=np.int64)
+    ids = np.asarray(queue_ids, dtype=np.int64)
+    msg = np.repeat(np.arange(len(off) - 1, dtype=np.int64), np.diff(off))
+    order = np.argsort(ids, kind="stable")
+    q_off = np.zeros(n_queues + 1, dtype=np.uint32)
+    q_off[1:] = np.cumsum(np.bincount(ids, minlength=n_queues))
+    return q_off, msg[order].astype(np.uint32)
+
+
+def publish_flags(offsets, queue_ids, any_durable, pub_flags, exchange_durable, queue_has_consumer=None):
+    """-> (refer_count uint32[n], flags uint8[n]): bit 0 isPersistent (EX:302), bit 1 isNonRouted (mandatory && no
+    queue), bit 2 isNonDeliverable (immediate && no matched queue has a consumer) (EX:319-330)"""
+    off = np.asarray(offsets, dtype=np.int64)
+    n = len(off) - 1
+    cnt = np.diff(off)
+    pf = np.zeros(n, dtype=np.uint8) if pub_flags is None else np.asarray(pub_flags, dtype=np.uint8)
+    out = np.zeros(n, dtype=np.uint8)
+    out |= (bool(exchange_durable) & ((pf & 4) != 0) & (np.asarray(any_durable) != 0)).astype(np.uint8)
+    out |= ((((pf & 1) != 0) & (cnt == 0)).astype(np.uint8) << 1)
+    has = np.zeros(n, dtype=bool)
+    if queue_has_consumer is not None and len(queue_ids):
+        hc = np.asarray(queue_has_consumer)[np.asarray(queue_ids, dtype=np.int64)] != 0
+        msg = np.repeat(np.arange(n), cnt)
+        has = np.bincount(msg, weights=hc, minlength=n) > 0
+    out |= ((((pf & 2) != 0) & ~has).astype(np.uint8) << 2)
+    return cnt.astype(np.uint32), out
