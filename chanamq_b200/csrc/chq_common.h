@@ -100,7 +100,8 @@ struct AtomRec {          // 32 B
 struct AllGroup {         // 32 B: the `all` bindings with one and the same atom set
   uint32_t atoms_off, n_atoms;            // into all_atoms (ascending)
   uint32_t list_off, list_len, flags;
-  uint32_t pad[3];
+  uint32_t sig_lo, sig_hi;                // bit (atom & 63) set for every atom of the set: a message whose own
+  uint32_t pad;                           // signature lacks one of these bits cannot satisfy the group
 };
 constexpr int kMaxHeaderFields = 64;      // known-name fields considered per message
 constexpr int kHeaderListsPerMessage = 16; // descriptor arena = this many matched lists per message on average

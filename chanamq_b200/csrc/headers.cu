@@ -21,23 +21,18 @@ namespace chq {
 
 namespace {
 
-__device__ uint32_t value_atom_lookup(const TableView& tv, uint32_t name_id, uint32_t tag, const uint8_t* v, uint32_t vl) {
-  uint64_t h = kFnvBasis ^ ((uint64_t)name_id << 8 | tag) * 0x9E3779B97F4A7C15ull;
-  uint64_t f8 = 0;
-  for (uint32_t i = 0; i < vl; ++i) {
-    const uint8_t c = __ldg(v + i);
-    h = fnv_step(h, c);
-    if (i < 8) f8 |= (uint64_t)c << (8 * i);
-  }
-  h = fin(h ^ ((uint64_t)vl << 40));
+// (name id, type tag, value bytes [q, q + vl)) -> atom id, 0 if no binding asks for that value
+__device__ uint32_t value_atom_lookup(const TableView& tv, uint32_t name_id, uint32_t tag, const uint32_t* __restrict__ ab,
+                                      uint32_t q, uint32_t vl, uint32_t rlo, uint32_t rhi, const uint8_t* __restrict__ v) {
   const uint32_t key = (name_id << 8) | tag;
-  uint32_t i = (uint32_t)h & tv.vdict_mask;
+  uint32_t f_lo = 0, f_hi = 0;
+  const uint32_t h = hash_bytes(ab, q, vl, rlo, rhi, kWordBasis ^ (key * 0x9E3779B1u), f_lo, f_hi);
+  uint32_t i = h & tv.vdict_mask;
   for (;;) {
     const uint4 a = ldg16(&tv.vdict[i]);
     const uint4 b = ldg16(reinterpret_cast<const uint8_t*>(&tv.vdict[i]) + 16);
     if (b.y == 0) return 0;
-    const uint64_t sh = ((uint64_t)a.y << 32) | a.x, sf = ((uint64_t)a.w << 32) | a.z;
-    if (sh == h && sf == f8 && b.x == vl && b.w == key) {
+    if (a.x == h && a.y == 0 && a.z == f_lo && a.w == f_hi && b.x == vl && b.w == key) {
       bool same = true;
       if (vl > 8) {
         const uint8_t* d = tv.vdict_bytes + b.z;
@@ -61,21 +56,22 @@ __global__ void __launch_bounds__(128) k_headers_match(const uint8_t* __restrict
   const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= n) return;  // only whole tail lanes leave: the warp-level allocation below uses the active mask
   const uint32_t b0 = off[m], b1 = hlen ? b0 + hlen[m] : off[m + 1];
+  // names and values are read as aligned 32-bit words (probe.cuh): offsets relative to the aligned base
+  const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(blob) & 3u);
+  const uint32_t* ab = reinterpret_cast<const uint32_t*>(blob - mis);
+  const uint32_t rlo = b0 + mis, rhi = b1 + mis;
   uint32_t atoms[2 * kMaxHeaderFields];
-  uint32_t seen[kMaxHeaderFields];
-  int na = 0, ns = 0;
+  uint32_t seen[kMaxHeaderFields];   // names with id >= 64 already met (the others are bits of seen_lo)
+  uint64_t seen_lo = 0;
+  int na = 0, ns = 0, ns_hi = 0;
   uint32_t status = 0;  // 3 = malformed table (the reference would have thrown while decoding), 4 = too many fields
   uint32_t p = b0;
   while (p < b1 && !status) {
     const uint32_t nl = __ldg(blob + p++);
     if (p + nl >= b1) { status = 3; break; }  // the name and at least a tag must fit
-    uint64_t h = kFnvBasis, f8 = 0;
-    for (uint32_t i = 0; i < nl; ++i) {
-      const uint8_t c = __ldg(blob + p + i);
-      h = fnv_step(h, c);
-      if (i < 8) f8 |= (uint64_t)c << (8 * i);
-    }
-    const uint32_t name_id = dict_lookup(tv, h, f8, nl, blob + p);
+    uint32_t f_lo = 0, f_hi = 0;
+    const uint32_t nh = hash_bytes(ab, p + mis, nl, rlo, rhi, kWordBasis, f_lo, f_hi);
+    const uint32_t name_id = word_lookup(tv, nh, f_lo, f_hi, nl, blob + p);
     p += nl;
     const uint32_t tag = __ldg(blob + p++);
     uint32_t vl = 0;
@@ -97,28 +93,46 @@ __global__ void __launch_bounds__(128) k_headers_match(const uint8_t* __restrict
     if ((uint64_t)p + vl > b1) { status = 3; break; }
     if (name_id != kUnknownWord) {
       bool dup = false;  // a name that occurs twice: the first occurrence counts (ValueReader.scala:71-72)
-      for (int i = 0; i < ns; ++i) dup = dup || seen[i] == name_id;
+      if (name_id < 64) {
+        dup = (seen_lo >> name_id) & 1ull;
+        seen_lo |= 1ull << name_id;
+      } else {
+        for (int i = 0; i < ns_hi; ++i) dup = dup || seen[i] == name_id;
+      }
       if (!dup) {
         if (ns == kMaxHeaderFields) { status = 4; break; }
-        seen[ns++] = name_id;
+        ++ns;
+        if (name_id >= 64) seen[ns_hi++] = name_id;
         const uint32_t pa = __ldg(tv.presence_atom + name_id);
         if (pa) atoms[na++] = pa;
-        const uint32_t va = value_atom_lookup(tv, name_id, tag, blob + p, vl);
+        const uint32_t va = value_atom_lookup(tv, name_id, tag, ab, p + mis, vl, rlo, rhi, blob + p);
         if (va) atoms[na++] = va;
       }
     }
     p += vl;
+  }
+  // the message's atoms in ascending order (insertion sort: a dozen entries) and their 64-bit signature
+  uint32_t sig_lo = 0, sig_hi = 0;
+  for (int i = 0; i < na; ++i) {
+    const uint32_t x = atoms[i];
+    if (x & 32u) sig_hi |= 1u << (x & 31u); else sig_lo |= 1u << (x & 31u);
+    int j = i;
+    for (; j > 0 && atoms[j - 1] > x; --j) atoms[j] = atoms[j - 1];
+    atoms[j] = x;
   }
   // Every matching list becomes one (offset, length) descriptor.  The matches are enumerated twice:
   // once to count, so that the warp can take one contiguous piece of the descriptor arena with a
   // single atomic, once to write.
   uint32_t k = 0, flags = 0;
   uint2* lists = nullptr;
+  constexpr uint32_t kKept = 24;  // descriptors found by the counting pass are kept, so most messages enumerate once
+  uint2 kept[kKept];
   auto for_each_match = [&](bool write) {
     uint32_t j = 0;
     auto emit = [&](uint32_t o, uint32_t l, uint32_t fl) {
       if (l == 0) return;
       if (write) lists[j] = make_uint2(o, l);
+      else if (j < kKept) kept[j] = make_uint2(o, l);
       ++j;
       flags |= fl;
     };
@@ -131,14 +145,17 @@ __global__ void __launch_bounds__(128) k_headers_match(const uint8_t* __restrict
       for (uint32_t g = a.w; g < all_end; ++g) {  // `all` groups anchored here: is every atom of the group satisfied?
         const uint8_t* gr = reinterpret_cast<const uint8_t*>(&tv.all_groups[g]);
         const uint4 ga = ldg16(gr);
-        bool ok = true;
+        const uint4 gb = ldg16(gr + 16);  // flags, signature
+        bool ok = (gb.y & ~sig_lo) == 0 && (gb.z & ~sig_hi) == 0;
+        // both atom lists ascend: one forward walk over the message's atoms finds them all or stops
+        int q = 0;
         for (uint32_t t = 0; t < ga.y && ok; ++t) {
           const uint32_t need = __ldg(tv.all_atoms + ga.x + t);
-          bool found = false;
-          for (int q = 0; q < na; ++q) found = found || atoms[q] == need;
-          ok = found;
+          while (q < na && atoms[q] < need) ++q;
+          ok = q < na && atoms[q] == need;
+          ++q;
         }
-        if (ok) emit(ga.z, ga.w, __ldg(reinterpret_cast<const uint32_t*>(gr) + 4));
+        if (ok) emit(ga.z, ga.w, gb.x);
       }
     }
     return j;
@@ -166,8 +183,12 @@ __global__ void __launch_bounds__(128) k_headers_match(const uint8_t* __restrict
   }
   if (k) {
     lists = desc_lists + start;
-    flags = 0;
-    for_each_match(true);
+    if (k <= kKept) {
+      for (uint32_t j = 0; j < k; ++j) lists[j] = kept[j];
+    } else {
+      flags = 0;
+      for_each_match(true);
+    }
   }
   if (status) { k = 0; flags = 0; start = 0; }
   desc_k[m] = k;

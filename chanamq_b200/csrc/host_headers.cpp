@@ -64,10 +64,6 @@ bool parse_fields(std::string_view t, std::vector<Field>* out) {
   return true;
 }
 
-uint64_t fnv_bytes(uint64_t h, std::string_view b) {
-  for (unsigned char c : b) h = fnv_step(h, c);
-  return h;
-}
 uint64_t first8(std::string_view w) {
   uint64_t f = 0;
   for (size_t i = 0; i < w.size() && i < 8; ++i) f |= (uint64_t)(unsigned char)w[i] << (8 * i);
@@ -85,16 +81,12 @@ bool valid_field_table(std::string_view t) { return parse_fields(t, nullptr); }
 
 // hash of a value atom; the device computes the same from (name id, tag, value bytes)
 uint64_t value_atom_hash(uint32_t name_id, uint8_t tag, std::string_view value) {
-  uint64_t h = kFnvBasis ^ ((uint64_t)name_id << 8 | tag) * 0x9E3779B97F4A7C15ull;
-  h = fnv_bytes(h, value);
-  return fin(h ^ ((uint64_t)value.size() << 40));
+  return bytes_hash(kWordBasis ^ (((name_id << 8) | tag) * 0x9E3779B1u), value);
 }
 
 void HostTable::compile_headers(CompiledTable& out) const {
   out.headers_mode = true;
   out.wstride = 4;
-  out.wdict.assign(1, WordSlot{});
-  out.wdict_off.assign(1, 0);
   out.tags.assign(kBucketSlots, 0);
   out.slot_group.assign(kBucketSlots, kNone);
   out.groups.assign(1, Group{});
@@ -188,6 +180,10 @@ void HostTable::compile_headers(CompiledTable& out) const {
       ag.atoms_off = (uint32_t)out.all_atoms.size();
       ag.n_atoms = (uint32_t)set->size();
       out.all_atoms.insert(out.all_atoms.end(), set->begin(), set->end());
+      uint64_t sig = 0;
+      for (uint32_t at : *set) sig |= 1ull << (at & 63u);
+      ag.sig_lo = (uint32_t)sig;
+      ag.sig_hi = (uint32_t)(sig >> 32);
       put_list(g.first, &ag.list_off, &ag.list_len);
       ag.flags = (g.second ? kAnyDurable : 0) | kShared;
       out.all_groups.push_back(ag);
@@ -199,22 +195,31 @@ void HostTable::compile_headers(CompiledTable& out) const {
   if (out.qlist.empty()) out.qlist.push_back(0);
   out.n_heads = n_atoms;
 
-  // field-name dictionary (the word dictionary's layout and hash)
+  // field-name dictionary (the word dictionary's layout and hash: 16-byte slots, one load per probe)
   auto dict_put = [](std::vector<DictSlot>& tab, const DictSlot& s) {
     uint32_t i = (uint32_t)s.hash & ((uint32_t)tab.size() - 1);
     while (tab[i].id != 0) i = (i + 1) & ((uint32_t)tab.size() - 1);
     tab[i] = s;
   };
-  out.dict.assign(pow2_at_least(std::max<uint64_t>(2, names.size() * 2)), DictSlot{});
-  for (auto& kv : names) {
-    DictSlot s{};
-    s.hash = fin(fnv_bytes(kFnvBasis, kv.first) ^ ((uint64_t)kv.first.size() << 56));
-    s.first8 = first8(kv.first);
-    s.len = (uint32_t)kv.first.size();
-    s.id = kv.second;
-    s.byte_off = (uint32_t)out.dict_bytes.size();
-    if (kv.first.size() > 8) out.dict_bytes.insert(out.dict_bytes.end(), kv.first.begin(), kv.first.end());
-    dict_put(out.dict, s);
+  out.dict.assign(1, DictSlot{});
+  {
+    const uint32_t nd = pow2_at_least(std::max<uint64_t>(2, names.size() * 2));
+    out.wdict.assign(nd, WordSlot{});
+    out.wdict_off.assign(nd, 0);
+    for (auto& kv : names) {
+      const uint32_t h = bytes_hash(kWordBasis, kv.first);
+      WordSlot s{};
+      s.first8 = first8(kv.first);
+      s.id = kv.second;
+      s.tag_len = (h & 0xFFFFFF00u) | (uint32_t)kv.first.size();
+      uint32_t i = h & (nd - 1);
+      while (out.wdict[i].id != 0) i = (i + 1) & (nd - 1);
+      out.wdict[i] = s;
+      if (kv.first.size() > 8) {
+        out.wdict_off[i] = (uint32_t)out.dict_bytes.size();
+        out.dict_bytes.insert(out.dict_bytes.end(), kv.first.begin(), kv.first.end());
+      }
+    }
   }
   if (out.dict_bytes.empty()) out.dict_bytes.push_back(0);
   out.presence_atom.assign(names.size() + 1, 0);

@@ -66,6 +66,8 @@ int HostTable::unbind_queue(std::string_view queue) {
   return CHQ_OK;
 }
 
+uint32_t bytes_hash(uint32_t seed, std::string_view w);
+
 namespace {
 
 uint32_t chunk32(std::string_view w, size_t at) {  // four bytes from `at`, little-endian, zero padded
@@ -73,15 +75,7 @@ uint32_t chunk32(std::string_view w, size_t at) {  // four bytes from `at`, litt
   for (size_t i = 0; i < 4 && at + i < w.size(); ++i) v |= (uint32_t)(unsigned char)w[at + i] << (8 * i);
   return v;
 }
-uint32_t word_hash(std::string_view w) {  // the tokeniser computes the same from aligned loads (kernels.cu)
-  uint32_t h = kWordBasis;
-  size_t at = 0;
-  do {
-    h = word_chunk(h, chunk32(w, at), chunk32(w, at + 4));
-    at += 8;
-  } while (at < w.size());
-  return word_fin(h, (uint32_t)w.size());
-}
+uint32_t word_hash(std::string_view w) { return bytes_hash(kWordBasis, w); }
 uint64_t first8(std::string_view w) {
   uint64_t f = 0;
   for (size_t i = 0; i < w.size() && i < 8; ++i) f |= (uint64_t)(unsigned char)w[i] << (8 * i);
@@ -101,6 +95,17 @@ struct GroupBuild {
 };
 
 }  // namespace
+
+// Hash of a byte string folded eight bytes at a time (the device side: hash_bytes in probe.cuh).
+uint32_t bytes_hash(uint32_t seed, std::string_view w) {
+  uint32_t h = seed;
+  size_t at = 0;
+  do {
+    h = word_chunk(h, chunk32(w, at), chunk32(w, at + 4));
+    at += 8;
+  } while (at < w.size());
+  return word_fin(h, (uint32_t)w.size());
+}
 
 void HostTable::compile(CompiledTable& out) const {
   out = CompiledTable();

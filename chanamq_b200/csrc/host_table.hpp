@@ -46,6 +46,8 @@ struct CompiledTable {
 // Java String.split("\\.") (QueueMatcher.scala:69,386,395,404): cut at every '.', drop trailing
 // empty words, keep leading/interior ones; no '.' at all gives the input back as one word.
 void java_split(std::string_view s, std::vector<std::string_view>& out);
+// hash of a word / field name / value: word_chunk over 8-byte chunks from `seed`, then word_fin with the length
+uint32_t bytes_hash(uint32_t seed, std::string_view w);
 
 class HostTable {
  public:

@@ -42,17 +42,6 @@ namespace chq {
 constexpr int kTokThreads = 256;
 constexpr int kTokStage = 8;   // rows of up to this many word ids are staged in shared memory and stored coalesced
 
-__device__ __forceinline__ uint32_t key_word32(const uint32_t* __restrict__ ab, uint32_t k, uint32_t rlo, uint32_t rhi) {
-  const uint32_t lo = 4 * k;
-  if (lo >= rhi) return 0;
-  if (lo >= rlo && lo + 4 <= rhi) return __ldg(ab + k);
-  uint32_t w = 0;
-  const uint8_t* b = reinterpret_cast<const uint8_t*>(ab);
-#pragma unroll
-  for (uint32_t j = 0; j < 4; ++j)
-    if (lo + j >= rlo && lo + j < rhi) w |= (uint32_t)__ldg(b + lo + j) << (8 * j);
-  return w;
-}
 // 0x80 in every byte of x that equals '.'
 __device__ __forceinline__ uint32_t dot_bytes(uint32_t x) {
   x ^= 0x2E2E2E2Eu;

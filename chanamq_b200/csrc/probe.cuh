@@ -43,6 +43,51 @@ __device__ uint32_t dict_lookup(const TableView& tv, uint64_t fnv, uint64_t f8, 
   }
 }
 
+// ---- bytes as aligned 32-bit words ---------------------------------------------------------------------
+// Byte offsets are relative to a 4-byte aligned base `ab`; [rlo, rhi) is the range that may be read.  A word
+// that straddles the edge of the range is assembled from byte loads, so nothing outside it is ever touched.
+__device__ __forceinline__ uint32_t key_word32(const uint32_t* __restrict__ ab, uint32_t k, uint32_t rlo, uint32_t rhi) {
+  const uint32_t lo = 4 * k;
+  if (lo >= rhi) return 0;
+  if (lo >= rlo && lo + 4 <= rhi) return __ldg(ab + k);
+  uint32_t w = 0;
+  const uint8_t* b = reinterpret_cast<const uint8_t*>(ab);
+#pragma unroll
+  for (uint32_t j = 0; j < 4; ++j)
+    if (lo + j >= rlo && lo + j < rhi) w |= (uint32_t)__ldg(b + lo + j) << (8 * j);
+  return w;
+}
+// eight bytes from byte offset q, little-endian (lo = bytes 0..3)
+__device__ __forceinline__ void load8(const uint32_t* __restrict__ ab, uint32_t q, uint32_t rlo, uint32_t rhi, uint32_t& lo,
+                                      uint32_t& hi) {
+  const uint32_t k = q >> 2, sh = (q & 3u) * 8u;
+  const uint32_t w0 = key_word32(ab, k, rlo, rhi), w1 = key_word32(ab, k + 1, rlo, rhi);
+  const uint32_t w2 = sh ? key_word32(ab, k + 2, rlo, rhi) : 0u;
+  lo = __funnelshift_r(w0, w1, sh);
+  hi = __funnelshift_r(w1, w2, sh);
+}
+// keeps the first `take` (0..8) bytes of (lo, hi)
+__device__ __forceinline__ void keep_bytes(uint32_t take, uint32_t& lo, uint32_t& hi) {
+  if (take >= 8) return;
+  if (take >= 4) hi &= (1u << (8 * (take - 4))) - 1u;
+  else { hi = 0; lo &= (1u << (8 * take)) - 1u; }
+}
+// word_fin(chunks of word_chunk over bytes [q, q + len), len): the hash the host computes with bytes_hash();
+// (f_lo, f_hi) = the first eight bytes, zero padded
+__device__ __forceinline__ uint32_t hash_bytes(const uint32_t* __restrict__ ab, uint32_t q, uint32_t len, uint32_t rlo,
+                                               uint32_t rhi, uint32_t seed, uint32_t& f_lo, uint32_t& f_hi) {
+  uint32_t h = seed, done = 0;
+  do {
+    uint32_t lo, hi;
+    load8(ab, q + done, rlo, rhi, lo, hi);
+    keep_bytes(len - done, lo, hi);
+    if (done == 0) { f_lo = lo; f_hi = hi; }
+    h = word_chunk(h, lo, hi);
+    done += 8;
+  } while (done < len);
+  return word_fin(h, len);
+}
+
 // Routing-key word -> id (topic / direct tables): one 16-byte load per probe step.  h = word_fin(...),
 // (lo, hi) = the first 8 bytes, bytes = the whole word (read only to confirm a word longer than 8 bytes).
 __device__ __forceinline__ uint32_t word_lookup(const TableView& tv, uint32_t h, uint32_t lo, uint32_t hi, uint32_t len,
