@@ -194,20 +194,26 @@ __global__ void __launch_bounds__(1024) k_fan_sort_big(const uint32_t* __restric
   extern __shared__ uint32_t smem_bm[];
   __shared__ uint32_t wtot[32];
   const uint32_t words = (n + 31) / 32;
-  uint32_t* bm = bitmaps ? bitmaps + (size_t)blockIdx.x * words : smem_bm;
+  // word w of the bitmap sits at w + w / 32: every thread reads a run of consecutive words below, and the skew
+  // keeps the 32 runs of a warp in different shared-memory banks
+  const uint32_t phys_words = words + words / 32 + 1;
+  uint32_t* bm = bitmaps ? bitmaps + (size_t)blockIdx.x * phys_words : smem_bm;
+  auto at = [](uint32_t w) { return w + (w >> 5); };
   const uint32_t per = (words + blockDim.x - 1) / blockDim.x;  // consecutive words per thread
   for (uint32_t k = blockIdx.x; k < *n_big; k += gridDim.x) {
     const uint32_t q = big[k], a = q_offsets[q], len = q_offsets[q + 1] - a;
-    for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) bm[i] = 0;
+    for (uint32_t i = threadIdx.x; i < phys_words; i += blockDim.x) bm[i] = 0;
     __syncthreads();
+    // (combining the bits of neighbouring lanes before the atomic — match_any or a segmented shuffle scan — was
+    // measured and is slower than the plain shared-memory atomics)
     for (uint32_t i = threadIdx.x; i < len; i += blockDim.x) {
       const uint32_t m = q_msgs[a + i];
-      atomicOr(bm + (m >> 5), 1u << (m & 31));
+      atomicOr(bm + at(m >> 5), 1u << (m & 31));
     }
     __syncthreads();
     const uint32_t w0 = threadIdx.x * per, w1 = min(w0 + per, words);
     uint32_t cnt = 0;
-    for (uint32_t i = w0; i < w1; ++i) cnt += __popc(bm[i]);
+    for (uint32_t i = w0; i < w1; ++i) cnt += __popc(bm[at(i)]);
     uint32_t incl = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -220,7 +226,7 @@ __global__ void __launch_bounds__(1024) k_fan_sort_big(const uint32_t* __restric
     for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) wbase += wtot[w];
     uint32_t out = a + wbase + incl - cnt;
     for (uint32_t i = w0; i < w1; ++i)
-      for (uint32_t bits = bm[i]; bits; bits &= bits - 1) q_msgs[out++] = i * 32 + (__ffs(bits) - 1);
+      for (uint32_t bits = bm[at(i)]; bits; bits &= bits - 1) q_msgs[out++] = i * 32 + (__ffs(bits) - 1);
     __syncthreads();
   }
 }
@@ -301,7 +307,8 @@ int32_t chq_fanout_device(const uint32_t* d_offsets, const uint32_t* d_queue_ids
   cudaStream_t st = (cudaStream_t)stream;
   const uint32_t n_tiles = (n_queues + kScanTileFan - 1) / kScanTileFan;
   // bitmap of the long-range sort: shared memory if the batch fits, else global
-  const size_t bm_bytes = (size_t)((n + 31) / 32) * 4;
+  const size_t bm_words = (size_t)((n + 31) / 32) + ((n + 31) / 32) / 32 + 1;  // skewed layout, see k_fan_sort_big
+  const size_t bm_bytes = bm_words * 4;
   static int smem_ok[64] = {};  // 0 unknown, 1 opted in, -1 not available
   if (smem_ok[dev & 63] == 0)
     smem_ok[dev & 63] = cudaFuncSetAttribute(k_fan_sort_big, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) == cudaSuccess ? 1 : -1;
@@ -312,7 +319,7 @@ int32_t chq_fanout_device(const uint32_t* d_offsets, const uint32_t* d_queue_ids
   if ((rc = fgrow(&sc.cursor, &sc.cursor_cap, (size_t)n_queues + 1))) return rc;
   if ((rc = fgrow(&sc.tiles, &sc.tiles_cap, (size_t)n_tiles + 2))) return rc;
   if ((rc = fgrow(&sc.big, &sc.big_cap, (size_t)n_queues + 1))) return rc;
-  if (!bm_smem && (rc = fgrow(&sc.bitmaps, &sc.bitmaps_cap, (size_t)big_ctas * ((n + 31) / 32) + 1))) return rc;
+  if (!bm_smem && (rc = fgrow(&sc.bitmaps, &sc.bitmaps_cap, (size_t)big_ctas * bm_words + 1))) return rc;
   uint32_t* n_big = sc.tiles + n_tiles;
   uint32_t* bad = sc.tiles + n_tiles + 1;
   FCU(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
