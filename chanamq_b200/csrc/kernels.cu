@@ -396,8 +396,8 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   else if (overflow) cls = 2;
   else if (p.desc_k && k > p.max_slots && k <= (uint32_t)kRouteSmall && ub <= (uint32_t)kRouteSmall) { cls = 4; cnt = ub; }
   else if (k <= 1) cnt = ub;
-  else if (k > p.max_slots || (dedup && ub - mxlen > p.max_small)) cls = 2;
-  else if (ub - mxlen > p.max_small) { cls = 3; cnt = ub; }
+  else if (k > p.max_slots) cls = 2;
+  else if (ub - mxlen > p.max_small) { cls = 3; cnt = ub; }  // with dedup the count is taken below
   else if (dedup) cls = 1;
   else cnt = ub;
 
@@ -430,12 +430,14 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
                                                 true, sm.ws[warp], nullptr, 0, lane);
     if (lane == src) cnt = c;
   }
-  for (unsigned todo = __ballot_sync(kFull, cls == 1); todo; todo &= todo - 1) {
+  for (unsigned todo = __ballot_sync(kFull, cls == 1 || (cls == 3 && dedup)); todo; todo &= todo - 1) {
     const int src = __ffs(todo) - 1;
     const int kk = __shfl_sync(kFull, k, src);
+    const bool lng = __shfl_sync(kFull, cls, src) == 3;
     uint32_t o = 0, l = 0;
     if (lane < kk) { o = sm.loff[lane][warp * 32 + src]; l = sm.llen[lane][warp * 32 + src]; }
-    const uint32_t c = warp_union<false>(tv.qlist, o, l, kk, true, sm.ws[warp], nullptr, 0, 0, lane);
+    const uint32_t c = lng ? warp_union_long<false>(tv.qlist, o, l, kk, true, sm.ws[warp], nullptr, 0, lane)
+                           : warp_union<false>(tv.qlist, o, l, kk, true, sm.ws[warp], nullptr, 0, 0, lane);
     if (lane == src) cnt = c;
   }
   if (m >= p.n) return;
@@ -571,7 +573,7 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
     CHQ_CLK_ADD(2, 1, c);
   } else {
     if (lane >= kk) lo = ll = 0;
-    if (cl == 3) warp_union_long(p.qlist, lo, ll, kk, ws, p.ids, o, lane);
+    if (cl == 3) warp_union_long<true>(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, lane);
     else warp_union<true>(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, p.ids_cap, lane);
 #ifdef CHQ_CLOCKS
     uint32_t sum = ll, mx = ll;

@@ -57,11 +57,14 @@ __device__ void warp_bitonic_sort(uint32_t* a, uint32_t np, int lane) {
 
 // In-place removal of adjacent duplicates of a sorted array by one warp; returns the new length.
 __device__ uint32_t warp_unique(uint32_t* a, uint32_t n, int lane) {
-  uint32_t kept = 0;
+  uint32_t kept = 0, carry = 0;  // carry = the last entry of the previous 32 as it was before compaction
   for (uint32_t base = 0; base < n; base += 32) {
     const uint32_t i = base + lane;
     const uint32_t v = i < n ? a[i] : 0;
-    const bool keep = i < n && (i == 0 || a[i - 1] != v);
+    uint32_t prev = __shfl_up_sync(kFull, v, 1);
+    if (lane == 0) prev = carry;
+    const bool keep = i < n && (i == 0 || prev != v);
+    carry = __shfl_sync(kFull, v, 31);
     __syncwarp();
     const unsigned m = __ballot_sync(kFull, keep);
     if (keep) a[kept + __popc(m & ((1u << lane) - 1))] = v;
@@ -374,8 +377,12 @@ __device__ uint32_t warp_union(const uint32_t* __restrict__ qlist, uint32_t my_o
 // a step yields at least 32 ids (or everything that is left) and at most 32 per list.
 static_assert(2 * kRouteSmall >= 32 * (kRouteSlots - 1), "a block of short ids lives in WarpScratch::a..b");
 
-__device__ void warp_union_long(const uint32_t* __restrict__ qlist, uint32_t my_off, uint32_t my_len, int k,
-                                WarpScratch& ws, uint32_t* __restrict__ out, uint64_t pos, int lane) {
+// With `dedup` an id may sit in several lists: equal ids of different short lists always show up in the same
+// step (both are <= T and inside their windows), get neighbouring places in the block (ties go by list index)
+// and are collapsed there; a short id equal to a long one is dropped by the weave.  Returns the size of the union.
+template <bool WRITE>
+__device__ uint32_t warp_union_long(const uint32_t* __restrict__ qlist, uint32_t my_off, uint32_t my_len, int k, bool dedup,
+                                    WarpScratch& ws, uint32_t* __restrict__ out, uint64_t pos, int lane) {
   const uint32_t len_k = lane < k ? my_len : 0;
   uint32_t nb = len_k;
 #pragma unroll
@@ -434,11 +441,14 @@ __device__ void warp_union_long(const uint32_t* __restrict__ qlist, uint32_t my_
           for (int j2 = 0; j2 < k; ++j2) {
             const uint32_t* W = ws.win[j2];
             if (j2 == j || W[0] == kNone) continue;
-            // shown ids of list j2 below x: at most 31 (a full window ends at or above T >= x, a partial one in kNone)
+            // shown ids of list j2 below x (or equal to it, for the lists before j: equal ids keep list order);
+            // at most 31 below (a full window ends at or above T >= x, a partial one in kNone), 32 only with a tie
+            const uint32_t xx = (dedup && j2 < j) ? x + 1 : x;  // ids < kNone, so x + 1 does not wrap
             uint32_t q = 0;
 #pragma unroll
             for (int step = 16; step; step >>= 1)
-              if (W[q + step - 1] < x) q += step;
+              if (W[q + step - 1] < xx) q += step;
+            if (q == 31 && W[31] < xx) q = 32;
             rank += q;
           }
           if (go) S[rank] = x;
@@ -450,6 +460,7 @@ __device__ void warp_union_long(const uint32_t* __restrict__ qlist, uint32_t my_
         blk_t = 0;
         more = __ballot_sync(kFull, len_s != cur) != 0;
         __syncwarp();
+        if (dedup) blk_n = warp_unique(S, emitted, lane);
       }
       const uint32_t s = (blk_t + lane < blk_n) ? S[blk_t + lane] : kNone;
       const bool inr = s <= bmax;  // in-range lanes form a prefix (the block ascends; ids < kNone)
@@ -463,19 +474,23 @@ __device__ void warp_union_long(const uint32_t* __restrict__ qlist, uint32_t my_
           if (probe < s) p += step;
         }
       }
-      if (inr) out[pos + c0 + p + kept_total + __popc(m_in & ((1u << lane) - 1))] = s;
-      // every long id moves up by the short ids below it
+      const bool in_long = __shfl_sync(kFull, b, p) == s;  // (every lane takes part in the shuffle)
+      const bool keep = inr && !(dedup && in_long);        // an id the long list has too is dropped
+      const unsigned km = __ballot_sync(kFull, keep);
+      if (WRITE && keep) out[pos + c0 + p + kept_total + __popc(km & ((1u << lane) - 1))] = s;
+      // every long id moves up by the kept short ids below it
       const uint32_t q = lanes_below(inr ? s : kNone, b);
-      shift += __popc(m_in & (q >= 32 ? kFull : ((1u << q) - 1)));
+      shift += __popc(km & (q >= 32 ? kFull : ((1u << q) - 1)));
       const uint32_t n_in = __popc(m_in);
-      kept_total += n_in;
+      kept_total += __popc(km);
       blk_t += n_in;
       if (n_in < 32 && blk_t < blk_n) break;  // the next short id lies beyond this chunk
     }
-    if (valid) out[pos + i + kept0 + shift] = b;
+    if (WRITE && valid) out[pos + i + kept0 + shift] = b;
     if (tail) break;
   }
   __syncwarp();
+  return nb + kept_total;
 }
 
 // Union of k <= 32 lists holding at most 32 ids together, given as (offset, length) descriptors in global
