@@ -27,6 +27,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--mode", default="compat", choices=["compat", "spec"])
+    ap.add_argument("--merge", default="owned", choices=["owned", "replicated"],
+                    help="owned: ids by all-to-all, each rank merges its message range; replicated: all-gather, every rank merges all")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -50,25 +52,41 @@ def main():
     d_off = torch.from_numpy(off.view(np.int32).copy()).to(dev)
     slice_cap = int(n * 160 / world * 1.25) + 1024
     out_cap = n * 160
-    total = 0
+    def step():
+        if a.merge == "owned":   # ids by all-to-all, every rank merges the message range it owns
+            _, _, _, ids, _ = sm.route_device_owned(d_blob, d_off, n, slice_cap, out_cap // world + 1024)
+        else:                    # ids by all-gather, every rank merges everything
+            _, ids, _, _ = sm.route_device(d_blob, d_off, n, slice_cap, out_cap)
+        return ids
+
     for _ in range(a.warmup):
-        out_off, out_ids, out_dur, _ = sm.route_device(d_blob, d_off, n, slice_cap, out_cap)
-        total = len(out_ids)
+        out_ids = step()
     dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(a.steps):
-        sm.route_device(d_blob, d_off, n, slice_cap, out_cap)
+        step()
     e1.record()
     torch.cuda.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1) / a.steps], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t[0])
-    chk = int(out_ids[: min(total, 1 << 20)].to(torch.int64).sum())
+    t = torch.tensor([e0.elapsed_time(e1) / a.steps, float(len(out_ids))], dtype=torch.float64, device=dev)
+    tmax = t.clone()
+    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    ms = float(tmax[0])
+    total = int(t[1]) if a.merge == "owned" else len(out_ids)   # owned: the ranks hold disjoint ranges
+    chk = int(out_ids[: min(len(out_ids), 1 << 20)].to(torch.int64).sum())
+    stages = None
+    if a.merge == "owned":   # one more step with CUDA-event marks between the stages (rank 0's view)
+        sm.trace = True
+        step()
+        stages = {k: round(v, 3) for k, v in sm.last_stages.items()}
     if rank == 0:
         print(json.dumps({
-            "metric": "routed msgs/sec (topic, %d bindings sliced over %d GPUs, NCCL all-gather of queue lists + merge)" % (a.bindings, world),
+            "metric": "routed msgs/sec (topic, %d bindings sliced over %d GPUs, %s)" % (
+                a.bindings, world, "all-to-all of the queue lists, merge sharded by message range" if a.merge == "owned"
+                else "NCCL all-gather of queue lists + merge on every GPU"),
+            "merge": a.merge, "stages_ms_rank0": stages,
             "value": n / (ms * 1e-3), "unit": "msgs/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "strong", "dtype": "u32", "data": "synthetic",
             "config": {"workload": "T(seed 4), %d bindings, binding i on GPU i mod %d, one batch of %d keys routed by all GPUs "

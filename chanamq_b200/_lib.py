@@ -63,6 +63,7 @@ def load_library():
         "chq_route_device_static": (i32, [vp, vp, vp, u32, vp, vp, u64, vp, vp, vp, vp, vp]),
         "chq_declare_queues": (i32, [vp, vp, vp, u32]),
         "chq_merge_slices_device": (i32, [i32, vp, vp, u64, vp, u32, u32, vp, vp, u64, vp, vp, vp, vp]),
+        "chq_merge_slices_device2": (i32, [i32, vp, vp, u64, vp, u32, u32, vp, vp, u64, vp, vp, vp, u32, vp]),
         "chq_decode": (i32, [vp, u64, vp, u32, vp, u64, C.POINTER(u64), vp, vp, vp]),
         "chq_decode_device": (i32, [vp, u64, vp, u32, vp, u64, vp, vp, vp, vp, vp, vp]),
         "chq_publish_keys_device": (i32, [vp, vp, u64, vp, vp, vp, vp, vp]),

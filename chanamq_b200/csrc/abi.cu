@@ -721,6 +721,14 @@ int32_t chq_merge_slices_device(int32_t device, const uint32_t* d_slice_offsets,
                                 const uint8_t* d_slice_durable, uint32_t n_slices, uint32_t n, uint32_t* d_offsets,
                                 uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable, uint64_t* d_total,
                                 int32_t* d_status, void* stream) {
+  return chq_merge_slices_device2(device, d_slice_offsets, d_slice_ids, slice_cap, d_slice_durable, n_slices, n, d_offsets,
+                                  d_queue_ids, ids_cap, d_any_durable, d_total, d_status, 0u, stream);
+}
+
+int32_t chq_merge_slices_device2(int32_t device, const uint32_t* d_slice_offsets, const uint32_t* d_slice_ids, uint64_t slice_cap,
+                                 const uint8_t* d_slice_durable, uint32_t n_slices, uint32_t n, uint32_t* d_offsets,
+                                 uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable, uint64_t* d_total,
+                                 int32_t* d_status, uint32_t flags, void* stream) {
   if (device < 0 || device >= 64 || !d_slice_offsets || !d_slice_ids || !d_slice_durable || !d_offsets || !d_any_durable ||
       !d_total || !d_status || n_slices == 0 || n_slices > (uint32_t)kRouteSlots)
     return fail(CHQ_E_ARG, "chq_merge_slices_device: bad argument (1..8 slices)");
@@ -768,6 +776,7 @@ int32_t chq_merge_slices_device(int32_t device, const uint32_t* d_slice_offsets,
   p.slice_durable = d_slice_durable;
   p.n_slices = n_slices;
   p.slice_cap = slice_cap;
+  p.slice_disjoint = (flags & CHQ_MERGE_DISJOINT) ? 1u : 0u;
   CU(launch_route(p, sms[device], st));
   CU(launch_finish(p.ctrl, d_status, st));
   return CHQ_OK;

@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
           GroupRec rec{};
           rec.list_off = (uint32_t)(r * p.slice_cap + a);
           rec.list_len = e - a;
-          rec.flags = kShared | (__ldg(p.slice_durable + (size_t)r * p.n + m) ? kAnyDurable : 0);
+          rec.flags = (p.slice_disjoint ? 0u : (uint32_t)kShared) | (__ldg(p.slice_durable + (size_t)r * p.n + m) ? kAnyDurable : 0);
           record(rec);
         } else if (__ldg(p.slice_durable + (size_t)r * p.n + m)) {
           flags |= kAnyDurable;

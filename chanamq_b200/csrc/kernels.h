@@ -49,6 +49,7 @@ struct RouteParams {
   const uint8_t* slice_durable;    // [n_slices][n]
   uint32_t n_slices;
   uint64_t slice_cap;
+  uint32_t slice_disjoint;   // no queue id occurs in two slices: the merge need not de-duplicate
   // descriptor mode (headers exchange): message m's lists are desc_lists[desc_start[m] + j], j < desc_k[m]
   const uint32_t* desc_k;          // null = not this mode
   const uint32_t* desc_start;      // message m's descriptors are desc_lists[desc_start[m] ...]

@@ -162,6 +162,13 @@ int32_t chq_merge_slices_device(int32_t device, const uint32_t* d_slice_offsets,
                                 const uint8_t* d_slice_durable, uint32_t n_slices, uint32_t n, uint32_t* d_offsets,
                                 uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable, uint64_t* d_total,
                                 int32_t* d_status, void* stream);
+/* The same with flags: CHQ_MERGE_DISJOINT = the caller knows that no queue is bound on two slices (true when
+ * every queue has a single binding), so the per-message unions need no de-duplication — about twice as fast. */
+enum { CHQ_MERGE_DISJOINT = 1 };
+int32_t chq_merge_slices_device2(int32_t device, const uint32_t* d_slice_offsets, const uint32_t* d_slice_ids, uint64_t slice_cap,
+                                const uint8_t* d_slice_durable, uint32_t n_slices, uint32_t n, uint32_t* d_offsets,
+                                uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable, uint64_t* d_total,
+                                int32_t* d_status, uint32_t flags, void* stream);
 
 /* ---- decode seam: FrameParser.onReceive (chana-mq-base/.../engine/FrameParser.scala:78-158) +
  *      CommandAssembler.onReceive (.../engine/CommandAssembler.scala:56-130) + Basic.Publish arguments

@@ -43,6 +43,14 @@ def main():
     ok = (np.array_equal(out_off.cpu().numpy().view(np.uint32), w_off) and
           np.array_equal(out_ids.cpu().numpy().view(np.uint32), w_ids) and np.array_equal(out_dur.cpu().numpy(), w_dur))
     print("rank %d/%d sharded route %s: %d keys -> %d ids" % (rank, world, "OK" if ok else "MISMATCH", n, len(w_ids)), flush=True)
+    # the same with the merge sharded by message range (all-to-all of the ids)
+    m0, m1, o_off, o_ids, o_dur = sm.route_device_owned(d_blob, d_off, n, slice_cap=4_000_000, out_cap=8_000_000)
+    a, b = int(w_off[m0]), int(w_off[m1])
+    ok2 = (np.array_equal(o_off.cpu().numpy().view(np.uint32), w_off[m0:m1 + 1] - w_off[m0]) and
+           np.array_equal(o_ids.cpu().numpy().view(np.uint32), w_ids[a:b]) and np.array_equal(o_dur.cpu().numpy(), w_dur[m0:m1]))
+    print("rank %d/%d owned-range route %s: messages [%d, %d) -> %d ids" % (rank, world, "OK" if ok2 else "MISMATCH", m0, m1, b - a),
+          flush=True)
+    ok = ok and ok2
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
