@@ -187,6 +187,8 @@ def run_ours(a, rank, world, local_rank):
     m.bind_many(*binds)
     m.commit()
     build_s = time.perf_counter() - t0
+    if os.environ.get("CHQ_MAX_SMALL"):  # experiment switch: where the staged merge hands over to warp_union_long
+        m.debug_limits(0, int(os.environ["CHQ_MAX_SMALL"]))
     st = m.stats()
 
     # ---- inputs: N_BATCHES distinct batches per rank, in pinned host memory and resident in HBM ----
