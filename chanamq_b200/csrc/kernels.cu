@@ -25,6 +25,9 @@
 #ifndef CHQ_MIN_CTAS
 #define CHQ_MIN_CTAS 8
 #endif
+#ifndef CHQ_LONG_MIN
+#define CHQ_LONG_MIN 32
+#endif
 #ifndef CHQ_LONG_K
 #define CHQ_LONG_K 5
 #endif
@@ -402,7 +405,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   else if (k > p.max_slots) cls = 2;
   // (measured: with up to CHQ_LONG_K = 5 lists warp_union_long beats the shared-memory rank merge from 33 short ids
   // on; with more lists its multi-way step, quadratic in the list count, loses)
-  else if (ub - mxlen > (k <= (uint32_t)CHQ_LONG_K ? min(p.max_small, 32u) : p.max_small)) { cls = 3; cnt = ub; }  // dedup: counted below
+  else if (ub - mxlen > (k <= (uint32_t)CHQ_LONG_K ? min(p.max_small, (uint32_t)CHQ_LONG_MIN) : p.max_small)) { cls = 3; cnt = ub; }  // dedup: counted below
   else if (dedup) cls = 1;
   else cnt = ub;
 

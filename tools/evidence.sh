@@ -11,6 +11,8 @@ python bench.py --impl reference > $O/bench_ref.json 2> $O/bench_ref.err
 python bench.py --mode spec --no-cpu-baseline > $O/bench_spec.json 2> $O/bench_spec.err
 python bench_decode.py > $O/bench_decode.json 2> $O/bench_decode.err
 python bench_headers.py > $O/bench_headers.json 2> $O/bench_headers.err
+python bench_decode.py --segments 1 > $O/bench_decode_one.json 2> $O/bench_decode_one.err
+python bench_fanout.py > $O/bench_fanout.json 2> $O/bench_fanout.err
 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $O/plain.log 2>&1 || exit 2
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $O/ncu_l.log 2>&1
 for k in write probe tokenize; do
