@@ -71,6 +71,8 @@ def load_library():
         "chq_fanout_device": (i32, [vp, vp, u32, u32, vp, vp, u64, vp, vp]),
         "chq_publish_flags_device": (i32, [vp, vp, vp, vp, u32, i32, vp, u32, vp, vp, vp]),
         "chq_fanout_last_error": (C.c_char_p, []),
+        "chq_deliver_encode_device": (i32, [vp, vp, u64, vp, vp, u32, u32, vp, u64, vp, vp, vp]),
+        "chq_encode_last_error": (C.c_char_p, []),
         "chq_host_alloc": (i32, [C.POINTER(vp), u64]),
         "chq_host_free": (i32, [vp]),
         "chq_stats": (i32, [vp, C.c_char_p, u32]),

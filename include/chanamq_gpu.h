@@ -246,6 +246,34 @@ int32_t chq_publish_flags_device(const uint32_t* d_offsets, const uint32_t* d_qu
                                  uint8_t* d_out_flags, void* stream);
 const char* chq_fanout_last_error(void);
 
+/* ---- delivery-side encode: Basic.Deliver + content header + body frames ----
+ * Replaces AMQCommand.render for deliveries (chana-mq-base/.../model/AMQCommand.scala:30-65; the method
+ * arguments of .../method/Basic.scala:189-205, AMQContentHeader.toFrame .../model/AMQContentHeader.scala:50-57,
+ * Frame.writeTo .../model/Frame.scala:220-226).  Delivery d sends the Basic.Publish that record `rec` of a decoded
+ * batch describes (chq_decode_device left d_bytes / d_recs on the device) to one consumer: METHOD frame
+ * (consumer tag, delivery tag, redelivered, exchange, routing key), HEADER frame (class 60, weight 0, bodySize, the
+ * publish's property bytes as they arrived) and the body re-cut into frames of at most frame_max - 8 payload bytes
+ * (frame_max 0: one frame).  Output d of the batch is d_out[d_out_offsets[d] .. d_out_offsets[d + 1]), in delivery
+ * order, ready to be written to the consumers' sockets.  Asynchronous on `stream`; *d_status = CHQ_OK,
+ * CHQ_E_OVERFLOW (out_cap too small: whole deliveries that do not fit are left out, d_out_offsets is complete) or
+ * CHQ_E_ARG (a delivery names a record that is not a decoded Basic.Publish; it gets zero bytes).
+ * The reference re-encodes the properties from its BasicProperties object; the copy made here is identical whenever
+ * that re-encoding is the identity (no repeated names and at most four entries per field table — from five entries
+ * on the reference emits its Map's hash order, which nothing pins). */
+typedef struct {
+  uint64_t delivery_tag;
+  uint32_t rec;          /* index into d_recs */
+  uint32_t ctag_off;     /* consumer tag = d_ctags[ctag_off .. ctag_off + ctag_len) */
+  uint16_t channel;
+  uint8_t ctag_len;
+  uint8_t redelivered;
+  uint32_t pad;
+} chq_delivery;          /* 24 bytes */
+int32_t chq_deliver_encode_device(const uint8_t* d_bytes, const chq_publish_rec* d_recs, uint64_t n_recs, const uint8_t* d_ctags,
+                                  const chq_delivery* d_deliveries, uint32_t n_del, uint32_t frame_max, uint8_t* d_out,
+                                  uint64_t out_cap, uint64_t* d_out_offsets, int32_t* d_status, void* stream);
+const char* chq_encode_last_error(void);
+
 /* pinned host memory for callers that want zero-copy staging (JNA: new Pointer(addr)) */
 int32_t chq_host_alloc(void** p, uint64_t bytes);
 int32_t chq_host_free(void* p);

@@ -273,3 +273,32 @@ def publish_flags(offsets, queue_ids, any_durable, pub_flags, exchange_durable, 
         has = np.bincount(msg, weights=hc, minlength=n) > 0
     out |= ((((pf & 2) != 0) & ~has).astype(np.uint8) << 2)
     return cnt.astype(np.uint32), out
+
+
+# ---- delivery-side encode (test infrastructure; small cases only: plain Python) ----
+def render_deliver(channel, consumer_tag, delivery_tag, redelivered, exchange, routing_key, header_payload, body, frame_max):
+    """AMQCommand.render for a Basic.Deliver (chana-mq-base/.../model/AMQCommand.scala:39-65): METHOD frame with the
+    arguments of .../method/Basic.scala:198-204, the HEADER frame AMQContentHeader.toFrame builds (class id, weight 0,
+    bodySize = body.length, then the properties: `header_payload` is that payload as the restated property writer of
+    tests/amqp_build.py produced it; only its weight and bodySize are overwritten here), BODY frames of at most
+    frameMax - NON_BODY_SIZE payload bytes (one frame of everything if frameMax == 0), every frame as Frame.writeTo does
+    (.../model/Frame.scala:220-226)."""
+    import struct
+
+    def frame(t, payload):
+        return struct.pack(">BHI", t, channel, len(payload)) + payload + b"\xce"
+
+    def shortstr(s):
+        return bytes([len(s)]) + s
+
+    args = (struct.pack(">HH", 60, 60) + shortstr(_b(consumer_tag)) + struct.pack(">Q", delivery_tag) + bytes([1 if redelivered else 0]) +
+            shortstr(_b(exchange)) + shortstr(_b(routing_key)))
+    out = frame(1, args)
+    hp = bytes(header_payload)
+    out += frame(2, hp[:2] + struct.pack(">HQ", 0, len(body)) + hp[12:])
+    bmax = len(body) if frame_max == 0 else frame_max - 8
+    off = 0
+    while off < len(body):
+        out += frame(3, body[off:off + bmax])
+        off += bmax
+    return out
