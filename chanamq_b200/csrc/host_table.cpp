@@ -1,6 +1,9 @@
 #include "host_table.hpp"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <unordered_map>
@@ -87,6 +90,14 @@ uint32_t pow2_at_least(uint64_t x) {
   return p;
 }
 
+struct VecHash {  // FNV-style hash of an encoded pattern
+  size_t operator()(const std::vector<uint32_t>& v) const {
+    uint64_t h = 0xCBF29CE484222325ull;
+    for (uint32_t x : v) h = (h ^ x) * 0x100000001B3ull;
+    return (size_t)(h ^ (h >> 29));
+  }
+};
+
 struct GroupBuild {
   uint32_t shape_key;  // index into the unsorted shape list
   std::vector<uint32_t> lits, rem;
@@ -108,21 +119,34 @@ uint32_t bytes_hash(uint32_t seed, std::string_view w) {
 }
 
 void HostTable::compile(CompiledTable& out) const {
+  // CHQ_COMPILE_TRACE=1 prints where the time of a commit goes (stderr)
+  const bool trace = getenv("CHQ_COMPILE_TRACE") != nullptr;
+  auto t_prev = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!trace) return;
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "compile: %-28s %7.3f s\n", what, std::chrono::duration<double>(now - t_prev).count());
+    t_prev = now;
+  };
   out = CompiledTable();
   out.n_bindings = live_.size();
   out.exact_rng.assign(3 * (kLenCap + 1), 0);
 
   // queue ids: rank of the name among the names that hold a binding, ascending by bytes
   {
-    std::set<std::string_view> q;
-    for (auto& t : live_) q.insert(std::get<1>(t));
-    for (auto& d : declared_) q.insert(d);
+    std::vector<std::string_view> q;
+    q.reserve(live_.size() + declared_.size());
+    for (auto& t : live_) q.push_back(std::get<1>(t));
+    for (auto& d : declared_) q.push_back(d);
+    std::sort(q.begin(), q.end());
+    q.erase(std::unique(q.begin(), q.end()), q.end());
     out.queue_names.assign(q.begin(), q.end());
   }
   std::unordered_map<std::string_view, uint32_t> qid;
   qid.reserve(out.queue_names.size() * 2);
   for (uint32_t i = 0; i < out.queue_names.size(); ++i) qid.emplace(out.queue_names[i], i);
 
+  lap("queue names and ids");
   if (type_ == CHQ_HEADERS && mode_ == CHQ_MODE_SPEC) {  // x-match on the arguments; the routing key plays no part
     compile_headers(out);
     return;
@@ -156,42 +180,38 @@ void HostTable::compile(CompiledTable& out) const {
     return;
   }
 
-  // pass 1: intern literal words (ids 1.. in byte order, so a rebuild gives the same table)
-  std::map<std::string_view, uint32_t> words;
+  // literal words are interned as they are met (ids 1..; the bindings are walked in key order, so a rebuild of
+  // the same set gives the same table)
+  std::unordered_map<std::string_view, uint32_t> words;
   std::vector<std::string_view> w;
   auto is_star = [](std::string_view s) { return s.size() == 1 && s[0] == '*'; };
   auto is_hash = [&](std::string_view s) { return spec && s.size() == 1 && s[0] == '#'; };
+  auto word_id = [&](std::string_view x) {
+    auto it = words.find(x);
+    if (it == words.end()) it = words.emplace(x, (uint32_t)words.size() + 1).first;
+    return it->second;
+  };
+
+  // reduce every pattern to (shape, literal tuple, remainder) and group equal ones
+  std::map<std::tuple<uint8_t, uint8_t, uint32_t>, uint32_t> shape_ids;  // (kind, len, mask)
+  std::vector<std::tuple<uint8_t, uint8_t, uint32_t>> shape_list;
+  std::unordered_map<std::vector<uint32_t>, uint32_t, VecHash> group_ids;  // encoded pattern -> group
+  group_ids.reserve(live_.size() * 2);
+  std::vector<GroupBuild> gb;
+  std::vector<uint32_t> pat, enc;
+  bool any_complex = false;
+  uint32_t max_len = 1, last_shape = kNone;
+  std::tuple<uint8_t, uint8_t, uint32_t> last_sk{};
   for (auto& t : live_) {
     std::string_view key = std::get<0>(t);
     if (split) java_split(key, w);
     else { w.clear(); w.push_back(key); }   // DirectMatcher: whole-key equality (QueueMatcher.scala:45-47)
-    for (auto& x : w)
-      if (!split || (!is_star(x) && !is_hash(x))) words.emplace(x, 0);
-  }
-  {
-    uint32_t id = 1;
-    for (auto& kv : words) kv.second = id++;
-    out.n_words = words.size();
-  }
-
-  // pass 2: reduce every pattern to (shape, literal tuple, remainder) and group equal ones
-  std::map<std::tuple<uint8_t, uint8_t, uint32_t>, uint32_t> shape_ids;  // (kind, len, mask)
-  std::vector<std::tuple<uint8_t, uint8_t, uint32_t>> shape_list;
-  std::map<std::vector<uint32_t>, uint32_t> group_ids;  // encoded pattern -> group
-  std::vector<GroupBuild> gb;
-  std::vector<uint32_t> pat, enc;
-  bool any_complex = false;
-  uint32_t max_len = 1;
-  for (auto& t : live_) {
-    std::string_view key = std::get<0>(t);
-    if (split) java_split(key, w);
-    else { w.clear(); w.push_back(key); }
     pat.clear();
     for (auto& x : w) {
       if (split && is_star(x)) pat.push_back(kStar);
       else if (is_hash(x)) {
         if (pat.empty() || pat.back() != kHash) pat.push_back(kHash);  // "#.#" == "#"
-      } else pat.push_back(words.at(x));
+      } else pat.push_back(word_id(x));
     }
     out.pattern_words += pat.size();
     size_t first_hash = std::find(pat.begin(), pat.end(), kHash) - pat.begin();
@@ -202,26 +222,34 @@ void HostTable::compile(CompiledTable& out) const {
     else if (first_hash < pat.size() && prefix <= (size_t)kMaxIndexedWords && first_hash + 1 == pat.size()) kind = kTail;
     else kind = kComplex;
     uint32_t mask = 0;
-    GroupBuild g;
     for (size_t p = 0; p < ip; ++p)
-      if (pat[p] != kStar) { mask |= 1u << p; g.lits.push_back(pat[p]); }
-    if (kind == kComplex) { g.rem.assign(pat.begin() + ip, pat.end()); any_complex = true; }
+      if (pat[p] != kStar) mask |= 1u << p;
+    if (kind == kComplex) any_complex = true;
     auto sk = std::make_tuple(kind, (uint8_t)ip, mask);
-    auto sit = shape_ids.find(sk);
-    if (sit == shape_ids.end()) {
-      sit = shape_ids.emplace(sk, (uint32_t)shape_list.size()).first;
-      shape_list.push_back(sk);
+    if (sk != last_sk || last_shape == kNone) {   // consecutive patterns (sorted by key) mostly share their shape
+      auto sit = shape_ids.find(sk);
+      if (sit == shape_ids.end()) {
+        sit = shape_ids.emplace(sk, (uint32_t)shape_list.size()).first;
+        shape_list.push_back(sk);
+      }
+      last_sk = sk;
+      last_shape = sit->second;
     }
-    g.shape_key = sit->second;
     max_len = std::max<uint32_t>(max_len, (uint32_t)ip);
     enc.clear();
-    enc.push_back(g.shape_key);
-    enc.insert(enc.end(), g.lits.begin(), g.lits.end());
+    enc.push_back(last_shape);
+    for (size_t p = 0; p < ip; ++p)
+      if (pat[p] != kStar) enc.push_back(pat[p]);
+    const size_t n_lits = enc.size() - 1;
     enc.push_back(kNone);
-    enc.insert(enc.end(), g.rem.begin(), g.rem.end());
+    if (kind == kComplex) enc.insert(enc.end(), pat.begin() + ip, pat.end());
     auto git = group_ids.find(enc);
     if (git == group_ids.end()) {
       git = group_ids.emplace(enc, (uint32_t)gb.size()).first;
+      GroupBuild g;
+      g.shape_key = last_shape;
+      g.lits.assign(enc.begin() + 1, enc.begin() + 1 + n_lits);
+      g.rem.assign(enc.begin() + 2 + n_lits, enc.end());
       gb.push_back(std::move(g));
     }
     GroupBuild& dst = gb[git->second];
@@ -229,6 +257,8 @@ void HostTable::compile(CompiledTable& out) const {
     dst.durable = dst.durable || std::get<2>(t);
   }
 
+  out.n_words = words.size();
+  lap("patterns to groups");
   // shapes: exact ones by length, then the '#' kinds by prefix length
   std::vector<uint32_t> order(shape_list.size());
   for (uint32_t i = 0; i < order.size(); ++i) order[i] = i;
@@ -274,9 +304,9 @@ void HostTable::compile(CompiledTable& out) const {
     for (uint32_t q : g.queues) queue_uses[q]++;
   }
   out.groups.resize(gb.size());
-  // chain heads keyed by (shape, literal tuple); group_ids iterates in encoded order, so groups
-  // that differ only in their remainder are adjacent
-  std::map<std::vector<uint32_t>, uint32_t> heads;
+  // chain heads keyed by (shape, literal tuple): groups that differ only in their remainder share one
+  std::unordered_map<std::vector<uint32_t>, uint32_t, VecHash> heads;
+  heads.reserve(gb.size() * 2);
   std::vector<std::pair<uint32_t, uint32_t>> head_hash;  // (hash, head group)
   for (uint32_t gi = 0; gi < gb.size(); ++gi) {
     GroupBuild& g = gb[gi];
@@ -321,6 +351,7 @@ void HostTable::compile(CompiledTable& out) const {
   }
   out.n_heads = head_hash.size();
 
+  lap("groups, lists, chain heads");
   // hash index over the chain heads: eight 16-bit tags per bucket, about 3/8 full, linear probing
   // by bucket; a bucket with an empty slot ends a probe sequence (no deletions: commit rebuilds)
   uint32_t nb = pow2_at_least(std::max<uint64_t>(1, (head_hash.size() + 2) / 3));
@@ -341,6 +372,7 @@ void HostTable::compile(CompiledTable& out) const {
     }
   }
 
+  lap("tag index");
   // word dictionary (open addressing on the word hash, at most half full)
   uint32_t nd = pow2_at_least(std::max<uint64_t>(2, words.size() * 2));
   out.dict.assign(1, DictSlot{});
