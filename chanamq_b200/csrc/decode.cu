@@ -403,12 +403,16 @@ __global__ void k_chunk_plan(const uint64_t* __restrict__ seg_off, uint32_t n_se
   if (threadIdx.x == 0) chunk_base[n_seg] = carry;
 }
 
-// one thread per chunk: guess the entry, walk
+// one warp (its first lane) per chunk: guess the entry, walk
 __global__ void k_chunk_walk(const uint8_t* __restrict__ b, const uint64_t* __restrict__ seg_off, uint32_t n_seg, uint64_t chunk,
                              const uint32_t* __restrict__ chunk_base, uint32_t max_chunks, uint32_t* __restrict__ cmd_off,
                              ChunkRes* __restrict__ res, uint32_t* __restrict__ chunk_seg, uint64_t* __restrict__ chunk_start,
                              uint64_t* __restrict__ chunk_count) {
-  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  // One chunk per WARP, walked by its first lane: the walk is a serial, branchy byte parser, and 32 of them in
+  // one warp run one after the other (measured: 6.5 active lanes per instruction, 3 % occupancy, 1.6 ms); with
+  // a warp each they run side by side and the SM hides their load latencies behind one another.
+  if (threadIdx.x & 31) return;
+  const uint32_t v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (v >= max_chunks) return;
   if (v >= chunk_base[n_seg]) { chunk_seg[v] = n_seg - 1; chunk_start[v] = 0; chunk_count[v] = 0; return; }
   uint32_t lo = 0, hi = n_seg;  // last segment whose first chunk <= v
@@ -661,7 +665,7 @@ int32_t chq_decode_device(const uint8_t* d_bytes, uint64_t len, const uint64_t* 
   if ((rc = grow(&sc.chunk_seg, &sc.cseg_cap, (size_t)max_chunks))) return rc;
   if ((rc = grow(&sc.chunk_start, &sc.cstart_cap, (size_t)max_chunks))) return rc;
   k_chunk_plan<<<1, 1024, 0, st>>>(d_seg_offsets, n_seg, chunk, sc.chunk_base);
-  k_chunk_walk<<<(max_chunks + 63) / 64, 64, 0, st>>>(d_bytes, d_seg_offsets, n_seg, chunk, sc.chunk_base, max_chunks, sc.cmd_off,
+  k_chunk_walk<<<(max_chunks + 3) / 4, 128, 0, st>>>(d_bytes, d_seg_offsets, n_seg, chunk, sc.chunk_base, max_chunks, sc.cmd_off,
                                                       sc.chunk_res, sc.chunk_seg, sc.chunk_start, sc.seg_count);
   k_chunk_validate<<<n_seg, 32, 0, st>>>(d_bytes, d_seg_offsets, n_seg, chunk, sc.chunk_base, sc.cmd_off, sc.chunk_res, sc.seg_count,
                                          d_seg_consumed, d_seg_err, d_seg_err_off);
