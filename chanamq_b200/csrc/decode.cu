@@ -334,43 +334,153 @@ __device__ uint64_t plausible_idle(const uint8_t* __restrict__ b, uint64_t p, ui
   return cs == kCmdDone ? next : p;
 }
 
-// First position in [from, to) that looks like an idle position and is followed by another one.
-__device__ uint64_t guess_idle(const uint8_t* __restrict__ b, uint64_t from, uint64_t to, uint64_t seg_end, uint32_t seg) {
+// First position in [from, to) that looks like an idle position and is followed by another one; only a 0x01
+// (METHOD) or a 0x08 (heartbeat) byte can start one.  By a whole warp: 512 bytes per step, 16 per lane; every lane tests the candidates among its own bytes in
+// ascending order, and the lowest lane that found one has the first plausible position of the stripe.
+__device__ uint64_t guess_idle_warp(const uint8_t* __restrict__ b, uint64_t from, uint64_t to, uint64_t seg_end, uint32_t seg,
+                                    int lane) {
   auto test = [&](uint64_t p) -> bool {
     const uint64_t q = plausible_idle(b, p, seg_end, seg);
     if (q == 0) return false;
-    if (q == p || q + 7 > seg_end) return true;           // runs into the end of the segment
+    if (q == p || q + 7 > seg_end) return true;
     return plausible_idle(b, q, seg_end, seg) != 0;
   };
-  uint64_t p = from;
-  // bytes up to the next 16-byte boundary one by one, then sixteen at a time: only a 0x01 (METHOD) or a 0x08
-  // (heartbeat) byte can start an idle position
-  for (; p < to && ((reinterpret_cast<uintptr_t>(b) + p) & 15u); ++p) {
-    const uint8_t c = __ldg(b + p);
-    if ((c == 1 || c == 8) && test(p)) return p;
-  }
-  for (; p + 16 <= to; p += 16) {
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(b + p));
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-    uint32_t any = 0;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const uint32_t a = w[i] ^ 0x01010101u, c = w[i] ^ 0x08080808u;
-      any |= ((a - 0x01010101u) & ~a & 0x80808080u) | ((c - 0x01010101u) & ~c & 0x80808080u);
-    }
-    if (!any) continue;
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-      for (int j = 0; j < 4; ++j) {
-        const uint32_t c = (w[i] >> (8 * j)) & 0xFFu;
-        if ((c == 1 || c == 8) && test(p + 4 * i + j)) return p + 4 * i + j;
+  const uint64_t mis = (reinterpret_cast<uintptr_t>(b) + from) & 15u;
+  for (uint64_t base = from - min(mis, from); base < to; base += 512) {
+    const uint64_t lo = base + 16 * (uint64_t)lane;
+    uint64_t found = kNoPos;
+    if (lo < to) {
+      uint32_t w[4] = {0, 0, 0, 0};
+      if (lo >= from && lo + 16 <= to && ((reinterpret_cast<uintptr_t>(b) + lo) & 15u) == 0) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(b + lo));
+        w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+      } else {
+        for (int i = 0; i < 16; ++i)
+          if (lo + i >= from && lo + i < to) w[i >> 2] |= (uint32_t)__ldg(b + lo + i) << (8 * (i & 3));
       }
-  }
-  for (; p < to; ++p) {
-    const uint8_t c = __ldg(b + p);
-    if ((c == 1 || c == 8) && test(p)) return p;
+      uint32_t any = 0;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t a = w[i] ^ 0x01010101u, c = w[i] ^ 0x08080808u;
+        any |= ((a - 0x01010101u) & ~a & 0x80808080u) | ((c - 0x01010101u) & ~c & 0x80808080u);
+      }
+      if (any) {
+        for (int i = 0; i < 16 && found == kNoPos; ++i) {
+          const uint32_t c = (w[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+          if ((c == 1 || c == 8) && lo + i >= from && lo + i < to && test(lo + i)) found = lo + i;
+        }
+      }
+    }
+    const unsigned hit = __ballot_sync(0xFFFFFFFFu, found != kNoPos);
+    if (hit) return __shfl_sync(0xFFFFFFFFu, found, __ffs(hit) - 1);
   }
   return kNoPos;
+}
+
+// Frame arithmetic of ONE command whose METHOD frame starts at pos (already known to be a complete, well-ended frame
+// that is not a heartbeat): where the command ends if its frames are in order and complete.  Nothing inside the
+// payloads is validated beyond what the arithmetic needs (class / method id, bodySize).  Returns false when anything is
+// out of the ordinary — wrong frame type, incomplete or badly ended frame, short payload, body overshoot — and the
+// caller then lets parse_command decide, so the outcome never depends on this shortcut.
+__device__ bool command_end_light(const uint8_t* __restrict__ b, uint64_t pos, uint64_t seg_end, uint64_t* next) {
+  FrameHdr f;
+  if (read_frame(b, pos, seg_end, f) != kFrameOk || f.type != 1 || f.size < 4) return false;
+  const uint32_t cls = (__ldg(b + pos + 7) << 8) | __ldg(b + pos + 8), mth = (__ldg(b + pos + 9) << 8) | __ldg(b + pos + 10);
+  pos += 8 + (uint64_t)f.size;
+  if (!has_content(cls, mth)) { *next = pos; return true; }
+  for (;;) {
+    if (read_frame(b, pos, seg_end, f) != kFrameOk) return false;
+    if (f.type != 8) break;
+    pos += 8 + (uint64_t)f.size;
+  }
+  if (f.type != 2 || f.size < 14) return false;
+  uint64_t bs = 0;
+  for (int i = 0; i < 8; ++i) bs = (bs << 8) | __ldg(b + pos + 7 + 4 + i);
+  int64_t remaining = (int64_t)bs;
+  pos += 8 + (uint64_t)f.size;
+  while (remaining > 0) {
+    if (read_frame(b, pos, seg_end, f) != kFrameOk) return false;
+    if (f.type == 3) {
+      remaining -= f.size;
+      if (remaining < 0) return false;
+    } else if (f.type != 8) return false;
+    pos += 8 + (uint64_t)f.size;
+  }
+  *next = pos;
+  return true;
+}
+
+// walk_chunk by a whole warp, with the same result.  Lane 0 runs ahead over up to 32 commands with the frame
+// arithmetic alone; then every lane validates one of them with the full parse_command (the expensive part: method
+// arguments, properties, field tables), all at once.  The first command that fails validation, or that the shortcut
+// would not vouch for, ends the batch: lane 0 gives it to parse_command and the walk stops or goes on as it says.
+__device__ void walk_chunk_warp(const uint8_t* __restrict__ b, uint64_t pos, uint64_t limit, uint64_t seg_end, uint32_t seg,
+                                uint32_t* __restrict__ list, ChunkRes& r, int lane) {
+  r.entry = pos; r.count = 0; r.err = 0; r.eoff = 0; r.stopped = 0; r.pad = 0;
+  bool done = false;
+  while (!done) {
+    // ---- lane 0: up to 32 command starts ----
+    uint32_t n = 0;
+    uint64_t p = pos;
+    bool unsure = false;   // the command at p needs the full parser (or is a frame-level stop)
+    if (lane == 0) {
+      while (n < 32 && p < limit) {
+        FrameHdr f;
+        const FrameStatus fs = read_frame(b, p, seg_end, f);
+        if (fs != kFrameOk) { unsure = true; break; }
+        if (f.type == 8) { p += 8 + (uint64_t)f.size; continue; }
+        uint64_t nx;
+        if (!command_end_light(b, p, seg_end, &nx)) { unsure = true; break; }
+        list[r.count + n] = (uint32_t)p;
+        ++n;
+        p = nx;
+      }
+    }
+    n = __shfl_sync(0xFFFFFFFFu, n, 0);
+    p = __shfl_sync(0xFFFFFFFFu, p, 0);
+    unsure = __shfl_sync(0xFFFFFFFFu, (int)unsure, 0) != 0;
+    __syncwarp();
+    // ---- every lane: full validation of one command ----
+    bool bad = false;
+    if ((uint32_t)lane < n) {
+      uint64_t nx, eo;
+      int32_t er;
+      bad = parse_command(b, list[r.count + lane], seg_end, seg, nullptr, &nx, &er, &eo) != kCmdDone;
+    }
+    const unsigned bad_mask = __ballot_sync(0xFFFFFFFFu, bad);
+    if (bad_mask) {  // the batch ends at its first invalid command, which lane 0 parses again below
+      n = (uint32_t)__ffs(bad_mask) - 1;
+      p = __shfl_sync(0xFFFFFFFFu, (uint64_t)list[r.count + n], 0);   // (lane 0 reads the list entry; all lanes get it)
+      unsure = true;
+    }
+    r.count += n;
+    pos = p;
+    if (unsure) {  // the sequential step at pos, exactly as walk_chunk does it
+      uint32_t stop = 0, adv = 0;
+      if (lane == 0) {
+        FrameHdr f;
+        const FrameStatus fs = read_frame(b, pos, seg_end, f);
+        if (fs == kFrameIncomplete) stop = 1;
+        else if (fs == kFrameNegative) { r.err = kErrThrown; r.eoff = pos; stop = 1; }
+        else if (fs == kFrameBadEnd) { r.err = kErrFrame; r.eoff = pos; stop = 1; }
+        else if (f.type == 8) pos += 8 + (uint64_t)f.size;
+        else {
+          uint64_t nx = pos;
+          const CmdStatus cs = parse_command(b, pos, seg_end, seg, nullptr, &nx, &r.err, &r.eoff);
+          if (cs != kCmdDone) { if (cs == kCmdIncomplete) { r.err = 0; r.eoff = 0; } stop = 1; }
+          else { list[r.count] = (uint32_t)pos; adv = 1; pos = nx; }
+        }
+      }
+      stop = __shfl_sync(0xFFFFFFFFu, stop, 0);
+      adv = __shfl_sync(0xFFFFFFFFu, adv, 0);
+      pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+      r.count += adv;
+      if (stop) { r.stopped = 1; done = true; }
+    }
+    if (pos >= limit) done = true;
+    __syncwarp();
+  }
+  r.exit = pos;
 }
 
 // chunks per segment -> chunk_base[n_seg + 1] (one block)
@@ -408,13 +518,17 @@ __global__ void k_chunk_walk(const uint8_t* __restrict__ b, const uint64_t* __re
                              const uint32_t* __restrict__ chunk_base, uint32_t max_chunks, uint32_t* __restrict__ cmd_off,
                              ChunkRes* __restrict__ res, uint32_t* __restrict__ chunk_seg, uint64_t* __restrict__ chunk_start,
                              uint64_t* __restrict__ chunk_count) {
-  // One chunk per WARP, walked by its first lane: the walk is a serial, branchy byte parser, and 32 of them in
-  // one warp run one after the other (measured: 6.5 active lanes per instruction, 3 % occupancy, 1.6 ms); with
-  // a warp each they run side by side and the SM hides their load latencies behind one another.
-  if (threadIdx.x & 31) return;
+  // One chunk per WARP: the walk is a serial, branchy byte parser, and 32 of them in one warp run one after the
+  // other (measured with a thread per chunk: 6.5 active lanes per instruction, 3 % occupancy, 1.6 ms).  With a warp
+  // each they run side by side, and inside the warp lane 0 follows the frame chain while all lanes validate the
+  // commands it finds (walk_chunk_warp).
+  const int lane = threadIdx.x & 31;
   const uint32_t v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (v >= max_chunks) return;
-  if (v >= chunk_base[n_seg]) { chunk_seg[v] = n_seg - 1; chunk_start[v] = 0; chunk_count[v] = 0; return; }
+  if (v >= chunk_base[n_seg]) {
+    if (lane == 0) { chunk_seg[v] = n_seg - 1; chunk_start[v] = 0; chunk_count[v] = 0; }
+    return;
+  }
   uint32_t lo = 0, hi = n_seg;  // last segment whose first chunk <= v
   while (hi - lo > 1) {
     const uint32_t mid = (lo + hi) >> 1;
@@ -423,13 +537,15 @@ __global__ void k_chunk_walk(const uint8_t* __restrict__ b, const uint64_t* __re
   const uint32_t s = lo, j = v - chunk_base[s];
   const uint64_t begin = seg_off[s], end = seg_off[s + 1];
   const uint64_t cs = begin + (uint64_t)j * chunk, ce = min(cs + chunk, end);
-  chunk_seg[v] = s;
-  chunk_start[v] = cs;
+  if (lane == 0) { chunk_seg[v] = s; chunk_start[v] = cs; }
   ChunkRes r;
-  const uint64_t entry = j == 0 ? begin : guess_idle(b, cs, ce, end, s);
+  uint64_t entry = begin;
+  if (j != 0) {
+    entry = guess_idle_warp(b, cs, ce, end, s, lane);
+  }
   if (entry == kNoPos) { r.entry = kNoPos; r.exit = kNoPos; r.eoff = 0; r.count = 0; r.err = 0; r.stopped = 0; r.pad = 0; }
-  else walk_chunk(b, entry, ce, end, s, cmd_off + chunk_list_base(cs, v), r);
-  res[v] = r;
+  else walk_chunk_warp(b, entry, ce, end, s, cmd_off + chunk_list_base(cs, v), r, lane);
+  if (lane == 0) res[v] = r;
 }
 
 // one warp per segment: the chain of chunk walks, checked 32 links at a time
