@@ -8,6 +8,7 @@ python bench.py --bindings 100000 --mode compat --steps 100 > $O/config2_topic_1
 python bench_headers.py > $O/config3_headers_50k.json 2> $O/config3.err
 python bench_decode.py > $O/config5_decode_1024seg.json 2> $O/config5a.err
 python bench_decode.py --segments 1 > $O/config5_decode_1seg.json 2> $O/config5b.err
+python bench_decode.py --route > $O/config5_decode_route.json 2> $O/config5c.err
 python bench_fanout.py > $O/next_fanout.json 2> $O/fanout.err
 python - $O <<'PY'
 import json, sys, glob, os
