@@ -77,7 +77,7 @@ for f in sorted(os.listdir(src)):
         try:
             d = json.loads(open(os.path.join(src, f)).read().strip().splitlines()[-1])
             print("%-26s %10.1f M %s  %.3f ms/step%s" % (f, d["value"] / 1e6, d.get("unit", ""), d.get("ms_per_step", 0),
-                                                        ("  e2e %.1f M" % (d["e2e"]["value"] / 1e6)) if "e2e" in d else ""))
+                                                        ("  e2e %.1f M" % (d["e2e"]["value"] / 1e6)) if d.get("e2e") else ""))
         except Exception as e:
             print(f, "unreadable", e)
 print(open(os.path.join(src, "pytest_gpu.log")).read().strip().splitlines()[-2:])
