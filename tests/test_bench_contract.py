@@ -1,0 +1,37 @@
+"""The reference arm of bench.py runs on host cores only, so its JSON contract can be checked here without a GPU:
+one line, the keys the driver reads, the metric and unit of BASELINE.json, and no device work claimed."""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_reference_arm_prints_one_contract_line():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1",
+                          "--bindings", "2000", "--batch", "4000", "--ref-sample", "2000"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [x for x in out.stdout.splitlines() if x.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    base = json.load(open(os.path.join(ROOT, "BASELINE.json")))
+    assert d["impl"] == "reference" and d["unit"] == "msgs/s" and d["higher_is_better"] is True
+    assert d["metric"].split(" at ")[0] in base["metric"]
+    for key in ("value", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert key in d, key
+    assert d["steps"] == 2 and d["warmup"] == 1 and d["value"] > 0 and d["vs_baseline"] is None
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": "msgs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "workload" in d["config"] and "model" not in d["config"]
+
+
+def test_product_arm_refuses_to_run_without_a_gpu():
+    """no CPU fallback: on a machine without CUDA the product arm must fail loudly, not time the oracle"""
+    import torch
+
+    if torch.cuda.is_available():
+        return
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "0", "--bindings", "1000",
+                          "--batch", "1000"], capture_output=True, text=True, timeout=300)
+    assert out.returncode != 0 and "no CUDA device" in (out.stderr + out.stdout)
