@@ -25,6 +25,9 @@
 #ifndef CHQ_MIN_CTAS
 #define CHQ_MIN_CTAS 8
 #endif
+#ifndef CHQ_PROBE_SORT
+#define CHQ_PROBE_SORT 1
+#endif
 #ifndef CHQ_LONG_MIN
 #define CHQ_LONG_MIN 32
 #endif
@@ -322,11 +325,31 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   RouteSmem& sm = *reinterpret_cast<RouteSmem*>(smem_raw);
   const TableView& tv = p.tv;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t m = blockIdx.x * kRouteThreads + tid;
+  uint32_t m = blockIdx.x * kRouteThreads + tid;
 
   uint32_t k = 0, ub = 0, mxlen = 0, flags = 0, cnt = 0, nw = 0;
-  const uint32_t* row = p.wid + (size_t)m * tv.wstride;
   if (m < p.n && !p.slice_offsets && !p.desc_k) nw = p.nwords[m];
+#if CHQ_PROBE_SORT
+  // The number of shapes a key is probed under grows with its word count (7 .. 22 for 3 .. 6 words), so the 128
+  // messages of the CTA are dealt to the threads in order of word count: the lanes of a warp then run loops of the
+  // same length.  Every thread still owns one message; only which one changes (everything below is indexed by m).
+  if (!p.slice_offsets && !p.desc_k) {
+    __shared__ uint32_t s_bin[10];
+    __shared__ uint16_t s_perm[kRouteThreads];
+    if (tid < 10) s_bin[tid] = 0;
+    __syncthreads();
+    const uint32_t bin = min(nw, 9u);
+    const uint32_t r = atomicAdd(&s_bin[bin], 1u);
+    __syncthreads();
+    uint32_t base = 0;
+    for (uint32_t x = 0; x < bin; ++x) base += s_bin[x];
+    s_perm[base + r] = (uint16_t)tid;
+    __syncthreads();
+    m = blockIdx.x * kRouteThreads + s_perm[tid];
+    nw = m < p.n ? p.nwords[m] : 0u;
+  }
+#endif
+  const uint32_t* row = p.wid + (size_t)m * tv.wstride;
   bool overflow = false;  // more tag hits than candidate slots: the slow path re-probes
   if (p.slice_offsets || p.desc_k) nw = m < p.n ? 1u : 0u;
   if (nw > 0 && !(p.debug & 2u)) {
@@ -413,7 +436,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   __syncwarp();
   for (unsigned todo = __ballot_sync(kFull, cls == 2); todo; todo &= todo - 1) {
     const int src = __ffs(todo) - 1;
-    const uint32_t mm = blockIdx.x * kRouteThreads + warp * 32 + src;
+    const uint32_t mm = __shfl_sync(kFull, m, src);
     uint64_t so;
     uint32_t fl;
     uint32_t c;
@@ -433,7 +456,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   }
   for (unsigned todo = __ballot_sync(kFull, cls == 4 && dedup); todo; todo &= todo - 1) {
     const int src = __ffs(todo) - 1;
-    const uint32_t mm = blockIdx.x * kRouteThreads + warp * 32 + src;
+    const uint32_t mm = __shfl_sync(kFull, m, src);
     const uint32_t c = warp_gather_small<false>(tv.qlist, p.desc_lists + __ldg(p.desc_start + mm), __shfl_sync(kFull, k, src),
                                                 true, sm.ws[warp], nullptr, 0, lane);
     if (lane == src) cnt = c;
