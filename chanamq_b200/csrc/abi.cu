@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -119,6 +120,7 @@ struct RouteSlot {
   PinBuf<uint8_t> r_durable, r_err;
   PinBuf<uint64_t> r_total;
   uint32_t n = 0;
+  uint64_t last_total = 0;   // ids of the previous batch on this slot: sizes d_ids for the next one
   bool busy = false;
   void release() {
     ws.release(); h_blob.release(); h_off.release(); d_blob.release(); d_off.release(); d_offsets.release();
@@ -134,8 +136,9 @@ struct RouteSlot {
 struct chq_table {
   HostTable host;
   CompiledTable ct;
-  bool committed = false;   // device copy is current: routing allowed
-  bool compiled = false;    // ct is current: queue names / stats valid
+  // written under mu by bind / commit (possibly on a Future's thread), read by the routing thread
+  std::atomic<bool> committed{false};   // device copy is current: routing allowed
+  std::atomic<bool> compiled{false};    // ct is current: queue names / stats valid
   bool host_only = false;   // device == -1: compile-only table for host-side checks, cannot route
   int device = 0, n_sms = 148;
   // device copy of the compiled table
@@ -299,7 +302,9 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   p.max_slots = t->max_slots;
   p.max_small = t->max_small;
   if (headers) { p.desc_k = ws.desc_k.p; p.desc_start = ws.desc_start.p; p.desc_flags = ws.desc_flags.p; p.desc_lists = ws.desc_lists.p; }
+#ifdef CHQ_DEBUG_SWITCHES  // experiment builds only: 1 = k_write writes nothing, 2 = k_probe probes nothing
   { const char* dbg = getenv("CHQ_DEBUG"); p.debug = dbg ? (uint32_t)atoi(dbg) : 0u; }
+#endif
   CU(launch_route(p, t->n_sms, st, pe ? pe + 2 : nullptr));
   if (pe) CU(cudaEventRecord(pe[4], st));
   CU(launch_finish(p.ctrl, d_status, st));
@@ -499,7 +504,9 @@ int32_t chq_route_submit(chq_table* t, int32_t slot, const uint8_t* keys_blob, c
   if ((rc = s.d_durable.ensure((size_t)n + 1))) return rc;
   if ((rc = s.d_err.ensure((size_t)n + 1))) return rc;
   if ((rc = s.d_total.ensure(2))) return rc;
-  if ((rc = s.d_ids.ensure((size_t)n * 16 + 1024))) return rc;
+  // the id buffer follows what the exchange produces: the last batch's total with headroom (first batch: a guess;
+  // a batch that overflows is run again by chq_route_wait with the exact size)
+  if ((rc = s.d_ids.ensure(std::max<size_t>((size_t)n * 16, (size_t)(s.last_total + s.last_total / 4)) + 1024))) return rc;
   if ((rc = s.r_total.ensure(2))) return rc;
   if ((rc = s.r_offsets.ensure((size_t)n + 1))) return rc;
   if ((rc = s.r_durable.ensure((size_t)n + 1))) return rc;
@@ -560,6 +567,7 @@ int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
   if (total) CU(cudaMemcpyAsync(s.r_ids.p, s.d_ids.p, total * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.st));
   CU(cudaStreamSynchronize(s.st));
   s.busy = false;
+  s.last_total = total;
   t->n_ids += total;
   out->n = s.n;
   out->offsets = s.r_offsets.p;
@@ -656,12 +664,15 @@ int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const 
     return fail(CHQ_E_ARG, "chq_route_device_static: bad argument");
   if (t->host_only) return fail(CHQ_E_CUDA, "chq_route_device_static: host-only table (device -1) cannot route");
   if (!t->committed) return fail(CHQ_E_NOT_COMMITTED, "chq_route_device_static: table has uncommitted binds");
+  if (t->ct.headers_mode)
+    return fail(CHQ_E_ARG, "chq_route_device_static: a headers exchange in CHQ_MODE_SPEC matches on the messages' header "
+                           "tables and needs a descriptor arena this entry point does not carry; use chq_route_device");
   if (n > kStaticMaxKeys)
     return fail(CHQ_E_ARG, "chq_route_device_static: more than CHQ_STATIC_MAX_KEYS keys in one call (split the batch, or "
                            "use chq_route_device, which allocates)");
   if ((uint64_t)n * t->tv.wstride > kStaticMaxWords)
     return fail(CHQ_E_ARG, "chq_route_device_static: keys x the table's word stride exceeds CHQ_STATIC_MAX_WORDS (tables "
-                           "with '#' inside a pattern keep 128 words per key: send fewer keys per call)");
+                           "with '#' inside a pattern keep 256 words per key: send fewer keys per call)");
   int rc = set_device(t);
   if (rc) return rc;
   unsigned char* base = nullptr;
@@ -715,6 +726,7 @@ int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const 
 // ---------------------------------------------------------------------------------------------
 namespace {
 Workspace g_merge_ws[64];
+std::mutex g_merge_mu[64];  // host side of the per-GPU workspace; calls on one GPU must not overlap on the device (header)
 }
 
 int32_t chq_merge_slices_device(int32_t device, const uint32_t* d_slice_offsets, const uint32_t* d_slice_ids, uint64_t slice_cap,
@@ -734,6 +746,7 @@ int32_t chq_merge_slices_device2(int32_t device, const uint32_t* d_slice_offsets
     return fail(CHQ_E_ARG, "chq_merge_slices_device: bad argument (1..8 slices)");
   if ((uint64_t)n_slices * slice_cap > 0xFFFFFFFFull) return fail(CHQ_E_ARG, "chq_merge_slices_device: gathered ids exceed 2^32-1");
   CU(cudaSetDevice(device));
+  std::lock_guard<std::mutex> lock(g_merge_mu[device]);
   Workspace& ws = g_merge_ws[device];
   cudaStream_t st = (cudaStream_t)stream;
   const uint32_t n_tiles = route_scan_tiles(n);

@@ -24,7 +24,7 @@ constexpr uint32_t kHash = 0xFFFFFFFDu;       // '#' inside a remainder (SPEC mo
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr int kMaxIndexedWords = 16;          // a shape indexes at most the first 16 words
 constexpr int kMaxKeyBytes = 255;             // AMQP shortstr (ValueReader.scala:35-39)
-constexpr int kMaxWords = 128;                // 255 bytes hold at most 128 non-trailing words
+constexpr int kMaxWords = 256;                // 255 bytes hold at most 255 words (empty interior words count: "a....b")
 constexpr int kLenCap = kMaxWords + 1;
 
 enum ShapeKind : uint8_t {

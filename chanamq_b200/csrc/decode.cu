@@ -19,6 +19,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <string>
 
 #include "kernels.h"
@@ -713,6 +714,11 @@ struct DecodeScratch {  // per device; grown on demand
   chq_publish_rec* d_recs = nullptr; size_t recs_cap = 0;
 };
 DecodeScratch g_scratch[64];
+// One scratch per GPU.  chq_decode (host buffers) holds the lock for its whole call, so concurrent broker threads
+// are simply served one after the other; chq_decode_device holds it while it grows the scratch and queues its
+// launches — the kernels of two device-level calls on different streams would still share the scratch, so those
+// calls must not overlap on one GPU (include/chanamq_gpu.h).
+std::recursive_mutex g_scratch_mu[64];
 
 template <typename T>
 int grow(T** p, size_t* cap, size_t need) {
@@ -740,6 +746,7 @@ int32_t chq_decode_device(const uint8_t* d_bytes, uint64_t len, const uint64_t* 
   int dev = 0;
   DCU(cudaGetDevice(&dev));
   DecodeScratch& sc = g_scratch[dev & 63];
+  std::lock_guard<std::recursive_mutex> lock(g_scratch_mu[dev & 63]);
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   // Segments are cut into chunks of this many bytes, one scanning thread each (CHQ_DECODE_CHUNK overrides the
@@ -815,6 +822,7 @@ int32_t chq_decode(const uint8_t* bytes, uint64_t len, const uint64_t* seg_offse
   int dev = 0;
   DCU(cudaGetDevice(&dev));  // fails loudly without a GPU: there is no CPU decoder in this library
   DecodeScratch& sc = g_scratch[dev & 63];
+  std::lock_guard<std::recursive_mutex> lock(g_scratch_mu[dev & 63]);
   int rc;
   if ((rc = grow(&sc.d_bytes, &sc.bytes_cap, (size_t)len + 16))) return rc;
   // one block: seg offsets (n+1), consumed (n), err_off (n), err (n, in 64-bit slots), misc (2)

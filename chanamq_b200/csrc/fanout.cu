@@ -19,6 +19,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
 #include <string>
 
 #include "../../include/chanamq_gpu.h"
@@ -140,9 +141,10 @@ __global__ void k_fan_scatter(const uint32_t* __restrict__ ids, const uint32_t* 
 // Ascending order inside every queue's range.  One warp per queue: up to 32 entries in registers, up to
 // kSortSmem in shared memory; longer ranges are left to k_fan_sort_big (their queue ids are appended to big[]).
 __global__ void __launch_bounds__(128) k_fan_sort_small(const uint32_t* __restrict__ q_offsets, uint32_t n_queues,
-                                                        uint32_t* __restrict__ q_msgs, uint32_t* __restrict__ big,
-                                                        uint32_t* __restrict__ n_big) {
+                                                        uint32_t* __restrict__ q_msgs, uint64_t q_cap,
+                                                        uint32_t* __restrict__ big, uint32_t* __restrict__ n_big) {
   __shared__ uint32_t buf[4][kSortSmem];
+  if ((uint64_t)q_offsets[n_queues] > q_cap) return;  // CHQ_E_OVERFLOW: the ranges reach past q_msgs, nothing there is touched
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
   for (uint32_t q = warp; q < n_queues; q += n_warps) {
@@ -191,6 +193,7 @@ __global__ void __launch_bounds__(128) k_fan_sort_small(const uint32_t* __restri
 __global__ void __launch_bounds__(1024) k_fan_sort_big(const uint32_t* __restrict__ q_offsets, uint32_t* __restrict__ q_msgs,
                                                        const uint32_t* __restrict__ big, const uint32_t* __restrict__ n_big,
                                                        uint32_t n, uint32_t* __restrict__ bitmaps) {
+  // (on CHQ_E_OVERFLOW k_fan_sort_small returns before it queues any range, so *n_big == 0 and nothing happens here)
   extern __shared__ uint32_t smem_bm[];
   __shared__ uint32_t wtot[32];
   const uint32_t words = (n + 31) / 32;
@@ -278,6 +281,7 @@ struct FanScratch {  // per device; grown on demand
   uint32_t* bitmaps = nullptr; size_t bitmaps_cap = 0; // [CTAs x ceil(n / 32)]
 };
 FanScratch g_fan[64];
+std::mutex g_fan_mu[64];  // host side of the scratch (growing it, queueing the launches); see chq_fanout_device
 
 template <typename T>
 int fgrow(T** p, size_t* cap, size_t need) {
@@ -304,6 +308,9 @@ int32_t chq_fanout_device(const uint32_t* d_offsets, const uint32_t* d_queue_ids
   FCU(cudaGetDevice(&dev));
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   FanScratch& sc = g_fan[dev & 63];
+  // One scratch per GPU: concurrent callers queue their launches one after the other here, but the kernels of two
+  // calls on different streams would still share it on the device — calls on one GPU must not overlap (header).
+  std::lock_guard<std::mutex> lock(g_fan_mu[dev & 63]);
   cudaStream_t st = (cudaStream_t)stream;
   const uint32_t n_tiles = (n_queues + kScanTileFan - 1) / kScanTileFan;
   // bitmap of the long-range sort: shared memory if the batch fits, else global
@@ -334,7 +341,7 @@ int32_t chq_fanout_device(const uint32_t* d_offsets, const uint32_t* d_queue_ids
   k_fan_scan_sums<<<1, 1024, 0, st>>>(sc.tiles, n_tiles);
   k_fan_scan_apply<<<n_tiles, 1024, 0, st>>>(sc.qcount, n_queues, sc.tiles, d_q_offsets, sc.cursor);
   k_fan_scatter<<<sms * 16, 256, 0, st>>>(d_queue_ids, d_offsets, n, n_queues, sc.cursor, d_q_msgs, q_cap);
-  k_fan_sort_small<<<sms * 16, 128, 0, st>>>(d_q_offsets, n_queues, d_q_msgs, sc.big, n_big);
+  k_fan_sort_small<<<sms * 16, 128, 0, st>>>(d_q_offsets, n_queues, d_q_msgs, q_cap, sc.big, n_big);
   k_fan_sort_big<<<big_ctas, 1024, bm_smem ? bm_bytes : 0, st>>>(d_q_offsets, d_q_msgs, sc.big, n_big, n,
                                                                  bm_smem ? nullptr : sc.bitmaps);
   k_fan_status<<<1, 1, 0, st>>>(d_offsets, n, q_cap, bad, d_status);

@@ -172,6 +172,7 @@ void HostTable::compile(CompiledTable& out) const {
       out.qlist.erase(std::unique(out.qlist.begin(), out.qlist.end()), out.qlist.end());
       g.list_off = 0;
       g.list_len = (uint32_t)out.qlist.size();
+      out.qlist.insert(out.qlist.end(), 4, kNone);  // room for the 16-byte units of a bulk copy
       g.flags = dur ? kAnyDurable : 0;
       out.groups.push_back(g);
       out.fanout_group = 0;
@@ -313,6 +314,9 @@ void HostTable::compile(CompiledTable& out) const {
     Group& d = out.groups[gi];
     d = Group{};
     d.shape = (uint16_t)new_shape[g.shape_key];
+    // lists worth a bulk copy start on a 16-byte boundary (k_write stages them with cp.async.bulk, weave.cuh)
+    if (g.queues.size() >= 8)
+      while (out.qlist.size() & 3u) out.qlist.push_back(kNone);
     d.list_off = (uint32_t)out.qlist.size();
     d.list_len = (uint32_t)g.queues.size();
     out.qlist.insert(out.qlist.end(), g.queues.begin(), g.queues.end());
@@ -350,6 +354,7 @@ void HostTable::compile(CompiledTable& out) const {
     }
   }
   out.n_heads = head_hash.size();
+  out.qlist.insert(out.qlist.end(), 4, kNone);  // a bulk copy moves whole 16-byte units: the last list may be read past its end
 
   lap("groups, lists, chain heads");
   // hash index over the chain heads: eight 16-bit tags per bucket, about 3/8 full, linear probing

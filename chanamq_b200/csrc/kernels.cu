@@ -21,6 +21,7 @@
 #include "kernels.h"
 #include "merge.cuh"
 #include "probe.cuh"
+#include "weave.cuh"
 
 #ifndef CHQ_MIN_CTAS
 #define CHQ_MIN_CTAS 8
@@ -28,14 +29,8 @@
 #ifndef CHQ_PROBE_SORT
 #define CHQ_PROBE_SORT 1
 #endif
-#ifndef CHQ_LONG_MIN
-#define CHQ_LONG_MIN 32
-#endif
-#ifndef CHQ_LONG_K
-#define CHQ_LONG_K 5
-#endif
 #ifndef CHQ_WRITE_CTAS
-#define CHQ_WRITE_CTAS 10
+#define CHQ_WRITE_CTAS 8
 #endif
 
 namespace chq {
@@ -327,7 +322,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   uint32_t m = blockIdx.x * kRouteThreads + tid;
 
-  uint32_t k = 0, ub = 0, mxlen = 0, flags = 0, cnt = 0, nw = 0;
+  uint32_t k = 0, ub = 0, mxlen = 0, mxidx = 0, flags = 0, cnt = 0, nw = 0;
   if (m < p.n && !p.slice_offsets && !p.desc_k) nw = p.nwords[m];
 #if CHQ_PROBE_SORT
   // The number of shapes a key is probed under grows with its word count (7 .. 22 for 3 .. 6 words), so the 128
@@ -352,12 +347,15 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   const uint32_t* row = p.wid + (size_t)m * tv.wstride;
   bool overflow = false;  // more tag hits than candidate slots: the slow path re-probes
   if (p.slice_offsets || p.desc_k) nw = m < p.n ? 1u : 0u;
-  if (nw > 0 && !(p.debug & 2u)) {
+#ifdef CHQ_DEBUG_SWITCHES
+  if (p.debug & 2u) nw = 0;
+#endif
+  if (nw > 0) {
     auto record = [&](const GroupRec& rec) {
       if (k < p.max_slots) { sm.loff[k][tid] = rec.list_off; sm.llen[k][tid] = rec.list_len; }
+      if (rec.list_len > mxlen) { mxlen = rec.list_len; mxidx = k; }
       ++k;
       ub += rec.list_len;
-      mxlen = max(mxlen, rec.list_len);
       flags |= rec.flags;
     };
     if (p.slice_offsets) {  // merge of per-slice results: the lists are given, nothing to probe
@@ -426,9 +424,8 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   else if (p.desc_k && k > p.max_slots && k <= (uint32_t)kRouteSmall && ub <= (uint32_t)kRouteSmall) { cls = 4; cnt = ub; }
   else if (k <= 1) cnt = ub;
   else if (k > p.max_slots) cls = 2;
-  // (measured: with up to CHQ_LONG_K = 5 lists warp_union_long beats the shared-memory rank merge from 33 short ids
-  // on; with more lists its multi-way step, quadratic in the list count, loses)
-  else if (ub - mxlen > (k <= (uint32_t)CHQ_LONG_K ? min(p.max_small, (uint32_t)CHQ_LONG_MIN) : p.max_small)) { cls = 3; cnt = ub; }  // dedup: counted below
+  // one long list + at most max_small other ids: k_write's staged weave (weave.cuh); more: warp_union_long
+  else if (ub - mxlen > p.max_small || ub >= (1u << 30)) { cls = 3; cnt = ub; }  // dedup: counted below
   else if (dedup) cls = 1;
   else cnt = ub;
 
@@ -482,7 +479,11 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   } else if (cls == 4) {
     lists[0] = make_uint2(__ldg(p.desc_start + m), 0u);  // where its descriptors start in the arena
   } else if (cnt > 0) {
-    for (uint32_t j = 0; j < k; ++j) lists[j] = make_uint2(sm.loff[j][tid], sm.llen[j][tid]);
+    // the longest list goes first: k_write streams it and weaves the others in
+    for (uint32_t j = 0; j < k; ++j) {
+      const uint32_t src = j == 0 ? mxidx : (j == mxidx ? 0u : j);
+      lists[j] = make_uint2(sm.loff[src][tid], sm.llen[src][tid]);
+    }
   }
 }
 
@@ -579,10 +580,11 @@ struct WriteCtx {  // the few fields of RouteParams it needs, by value (kernel p
   const uint32_t* scratch;
   uint32_t* ids;
   uint64_t ids_cap;
+  bool tma_ok;   // qlist is the table's own array (16-byte aligned, lists of 8+ ids start on 16-byte boundaries)
 };
 // (lo, ll) = this lane's entry of the message's list row (lane j < k: list j), fetched by the caller ahead of time.
-__device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws, uint32_t lo, uint32_t ll, uint32_t c,
-                                              uint32_t mt, uint64_t o, int lane) {
+__device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws, WeaveBuf& wb, uint32_t& phase, uint32_t lo,
+                                              uint32_t ll, uint32_t c, uint32_t mt, uint64_t o, int lane) {
   const int kk = mt & 0xFF, cl = (mt >> 8) & 0xF;
   CHQ_CLK_T0();
   if (cl == 2) {
@@ -605,7 +607,7 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
   } else {
     if (lane >= kk) lo = ll = 0;
     if (cl == 3) warp_union_long<true>(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, lane);
-    else warp_union<true>(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, p.ids_cap, lane);
+    else warp_weave(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, p.tma_ok, ws, wb, phase, p.ids + o, lane);
 #ifdef CHQ_CLOCKS
     uint32_t sum = ll, mx = ll;
     for (int d = 16; d; d >>= 1) { sum += __shfl_xor_sync(kFull, sum, d); mx = max(mx, __shfl_xor_sync(kFull, mx, d)); }
@@ -616,12 +618,20 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
 
 __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RouteParams p) {
   __shared__ WarpScratch ws_all[kRouteThreads / 32];
+  __shared__ WeaveBuf wb_all[kRouteThreads / 32];
   const TableView& tv = p.tv;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpScratch& ws = ws_all[warp];
+  WeaveBuf& wb = wb_all[warp];
+  uint32_t phase = 0;
+  weave_bar_init(wb, lane);
   const uint32_t n_chunks = (p.n + 31) / 32;
-  if (*p.total > 0xFFFFFFFFull || (p.debug & 1u)) return;  // offsets saturated: the launch reports CHQ_E_OVERFLOW
-  const WriteCtx wc{p.desc_lists, tv.qlist, p.mlist, p.scratch, p.ids, p.ids_cap};
+  if (*p.total > 0xFFFFFFFFull) return;  // offsets saturated: the launch reports CHQ_E_OVERFLOW
+#ifdef CHQ_DEBUG_SWITCHES
+  if (p.debug & 1u) return;
+#endif
+  const WriteCtx wc{p.desc_lists, tv.qlist, p.mlist, p.scratch, p.ids, p.ids_cap,
+                    !p.slice_offsets && (reinterpret_cast<uintptr_t>(tv.qlist) & 15u) == 0};
   // Two passes over the batch, 32 consecutive messages per sub-chunk.  Pass 0 sweeps the meta words (four
   // sub-chunks per grab) and does only the few messages with long results, so that the longest jobs start
   // first instead of being met by chance near the end of the kernel; pass 1 does everything else.
@@ -673,7 +683,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RoutePa
           todo &= todo - 1;
           const uint2 mine = row;
           row = row_of(todo);
-          write_message(wc, ws, mine.x, mine.y, __shfl_sync(kFull, cnt, src), __shfl_sync(kFull, meta, src),
+          write_message(wc, ws, wb, phase, mine.x, mine.y, __shfl_sync(kFull, cnt, src), __shfl_sync(kFull, meta, src),
                         __shfl_sync(kFull, pos, src), lane);
         }
       }

@@ -241,8 +241,13 @@ __device__ bool remainder_matches(const TableView& tv, uint32_t rem_off, uint32_
                                   uint32_t from, uint32_t nw) {
   const uint32_t r = rem_len;
   const uint32_t* rem = tv.rems + rem_off;
-  // reach bitset over states 0..r (r <= 128): 5 words
-  uint32_t cur[5] = {1u, 0, 0, 0, 0}, nxt[5];
+  // reach bitset over states 0..r: a pattern is at most 255 bytes, so r <= kMaxWords - 1 items
+  constexpr int kW = kMaxWords / 32 + 1;
+  if (r > (uint32_t)kMaxWords) return false;   // (the host never builds such a remainder)
+  uint32_t cur[kW], nxt[kW];
+#pragma unroll
+  for (int i = 0; i < kW; ++i) cur[i] = 0;
+  cur[0] = 1u;
   auto close = [&](uint32_t* st) {  // epsilon: a '#' can be skipped
     for (uint32_t s = 0; s < r; ++s)
       if ((st[s >> 5] >> (s & 31)) & 1u)
@@ -252,7 +257,7 @@ __device__ bool remainder_matches(const TableView& tv, uint32_t rem_off, uint32_
   for (uint32_t p = from; p < nw; ++p) {
     const uint32_t w = __ldg(row + p);
 #pragma unroll
-    for (int i = 0; i < 5; ++i) nxt[i] = 0;
+    for (int i = 0; i < kW; ++i) nxt[i] = 0;
     for (uint32_t s = 0; s < r; ++s) {
       if (!((cur[s >> 5] >> (s & 31)) & 1u)) continue;
       const uint32_t item = __ldg(rem + s);
@@ -261,7 +266,7 @@ __device__ bool remainder_matches(const TableView& tv, uint32_t rem_off, uint32_
     }
     close(nxt);
 #pragma unroll
-    for (int i = 0; i < 5; ++i) cur[i] = nxt[i];
+    for (int i = 0; i < kW; ++i) cur[i] = nxt[i];
   }
   return (cur[r >> 5] >> (r & 31)) & 1u;
 }

@@ -11,7 +11,13 @@
  * across the boundary; caller buffers are only read during the call; results point into
  * library-owned pinned memory that stays valid until the next route call on the same table.
  * Calls on ONE table must be serialised by the caller (one exchange = one actor = one thread in
- * the reference, ExchangeEntity.scala:107); different tables are independent.
+ * the reference, ExchangeEntity.scala:107); bind / unbind / commit may come from another thread (the
+ * reference binds from a Future callback, ExchangeEntity.scala:337-338) and are locked against each other.
+ * Different tables are independent.  The table-less device-level calls (chq_decode_device, chq_fanout_device,
+ * chq_merge_slices_device*) keep ONE scratch per GPU: any thread may call them, the library queues their
+ * launches one call after the other, but two such calls of the same kind whose kernels overlap on one GPU
+ * (different streams) would share that scratch — order them on the device (same stream, or an event).
+ * chq_decode (host buffers) holds the lock for its whole call and is safe from any number of threads.
  *
  * Paths relative to /root/reference/chana-mq-server/src/main/scala/chana/mq/amqp/server/.
  */
@@ -132,11 +138,13 @@ int32_t chq_route_device(chq_table* t, const uint8_t* d_keys_blob, const uint32_
  * device memory on every GPU that loads libchanagpu.so, held until the process exits.  Hence the limits:
  *   n                        <= CHQ_STATIC_MAX_KEYS  (65 536 keys per call)
  *   n x the table's word stride <= CHQ_STATIC_MAX_WORDS (524 288; the stride is 8 for ordinary tables,
- *                               so the first limit is the one that bites; it is 128 when a pattern has
- *                               '#' before its end, which leaves 4 096 keys per call)
+ *                               so the first limit is the one that bites; it is 256 when a pattern has
+ *                               '#' before its end or more than 16 words, which leaves 2 048 keys per call)
  * A larger request is refused with CHQ_E_ARG and a message saying which limit was hit; nothing is
  * launched.  The slow-path arena holds 1 Mi queue ids; a batch that needs more reports CHQ_E_SCRATCH
- * in *d_status, exactly like chq_route_device.
+ * in *d_status, exactly like chq_route_device.  A CHQ_HEADERS table in CHQ_MODE_SPEC is refused with
+ * CHQ_E_ARG: x-match routing needs a per-batch descriptor arena that this fixed array does not carry
+ * (such a table routed through here would silently match nothing); use chq_route_device for it.
  *
  * The first call on a device looks up the array's device address (cudaGetSymbolAddress) and sizes
  * the launch; make that first call during start-up, before any stream capture begins.

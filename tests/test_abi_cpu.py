@@ -51,7 +51,7 @@ def test_shapes_and_word_stride():
     st = m.stats()
     assert st["shapes"] == 6 and st["wstride"] == 8
     m.bind("a.#.b", "q")           # '#' in the middle: remainder verified by the NFA, all words kept
-    assert m.stats()["wstride"] == 128
+    assert m.stats()["wstride"] == 256   # 255 bytes hold up to 255 words
     c = GpuMatcher(CHQ_TOPIC, CHQ_MODE_COMPAT, device=-1)
     c.bind("a.#.b", "q")           # COMPAT: '#' is a word (QueueMatcher.scala:70)
     assert c.stats()["wstride"] == 4 and c.stats()["shapes"] == 1

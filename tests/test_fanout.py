@@ -99,6 +99,33 @@ def test_transpose_edge_cases():
 
 
 @pytest.mark.gpu
+def test_overflow_leaves_the_memory_behind_the_buffer_alone():
+    """CHQ_E_OVERFLOW: the ranges of the full counts reach past q_cap; neither the scatter nor the sorts may touch
+    what lies there (small DESCENDING sentinels: any sort over them would reorder them)"""
+    import torch
+
+    from chanamq_b200 import fanout as gf
+
+    rng = random.Random(77)
+    n, nq = 6000, 40
+    off, ids = _random_csr(rng, n, nq, [0, 3, 9])
+    total = int(off[-1])
+    cap, tail = total // 2, 4096
+    dev = torch.device("cuda:0")
+    d_off = torch.from_numpy(off.view(np.int32).copy()).to(dev)
+    d_ids = torch.from_numpy(np.ascontiguousarray(ids).view(np.int32).copy()).to(dev)
+    d_qoff = torch.full((nq + 1,), -1, dtype=torch.int32, device=dev)
+    sentinel = np.arange(tail, 0, -1, dtype=np.int32)
+    d_qmsg = torch.cat([torch.zeros(cap, dtype=torch.int32), torch.from_numpy(sentinel)]).to(dev)
+    d_st = torch.full((1,), 99, dtype=torch.int32, device=dev)
+    gf.fanout_device(d_off.data_ptr(), d_ids.data_ptr(), n, nq, d_qoff.data_ptr(), d_qmsg.data_ptr(), cap, d_st.data_ptr(),
+                     torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert int(d_st[0]) == -3
+    assert np.array_equal(d_qmsg.cpu().numpy()[cap:], sentinel)
+
+
+@pytest.mark.gpu
 def test_routed_batch_to_queue_lists_and_flags():
     """route 2^17 keys against a 100 k-binding table on the device, transpose, flags — all without leaving HBM"""
     import torch

@@ -102,6 +102,21 @@ def test_random_small_tables(mode, limits):
         check_csr_invariants(r, m.n_queues())
 
 
+@pytest.mark.parametrize("mode", [CHQ_MODE_COMPAT, CHQ_MODE_SPEC])
+def test_runs_of_dots_make_up_to_255_words(mode):
+    """a shortstr of 255 bytes holds up to 255 words when most of them are empty ("a....b"): patterns whose
+    remainder behind the 16 indexed words is ~200 items long, keys of 129..255 words"""
+    m, o = GpuMatcher(CHQ_TOPIC, mode), po.Oracle(po.TOPIC, po.SPEC if mode == CHQ_MODE_SPEC else po.COMPAT)
+    binds = [("#" + "." * 200 + "a", "q1", False), ("a" + "." * 128 + "b", "q2", True), ("a" + "." * 253 + "b", "q3", False),
+             ("a.#." + "." * 150 + "b", "q4", False), ("*" + "." * 128 + "*", "q5", False), ("a.#", "q6", False),
+             ("#.b", "q7", False), ("a" + "." * 100 + "#" + "." * 100 + "b", "q8", True)]
+    load_both(m, o, binds)
+    keys = ["a" + "." * 128 + "b", "a" + "." * 253 + "b", "x" + "." * 200 + "a", "." * 200 + "a", "a" + "." * 152 + "b",
+            "a" + "." * 201 + "b", "a" + "." * 127 + "b", "a" + "." * 129 + "b", "a.b", "a" + "." * 254, "." * 254 + "b"]
+    r = assert_same_routing(m, o, *pack(keys))
+    check_csr_invariants(r, m.n_queues())
+
+
 def test_long_patterns_and_long_keys_spec():
     """patterns beyond the 16 indexed words, '#' in the middle of long keys (word stride 128)"""
     rng = random.Random(5)

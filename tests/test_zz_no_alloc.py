@@ -2,15 +2,16 @@
 routing thread inside a latency budget, a process whose memory all belongs to a pool, a deployment
 that forbids allocation after start-up).  It runs the same kernels as chq_route_device with its
 scratch in a fixed array inside the library, so the check is simple: through the C ABI, on the same
-device buffers, it must give exactly what chq_route_device gives (integer work: equality) — on two
-calls in a row, because the array keeps the previous call's contents — and it must refuse, loudly and
-without launching anything, a batch larger than the array was sized for.
+device buffers, it must give exactly what chq_route_device gives AND what the CPU oracle gives (integer
+work: equality) — on two calls in a row, because the array keeps the previous call's contents — and it
+must refuse, loudly and without launching anything, a batch larger than the array was sized for and a
+table whose routing needs scratch the array does not carry (headers x-match).
 
 Collected last on purpose (file name): a failure here cannot hide another test's result under -x."""
 import numpy as np
 import pytest
 
-from chanamq_b200 import CHQ_MODE_SPEC, CHQ_TOPIC, ChqError, GpuMatcher
+from chanamq_b200 import CHQ_HEADERS, CHQ_MODE_SPEC, CHQ_TOPIC, ChqError, GpuMatcher
 from chanamq_b200 import _lib
 from chanamq_b200.workload import TopicWorkload, queue_names_packed
 
@@ -45,6 +46,9 @@ def test_static_scratch_entry_point_matches_the_allocating_one_twice_in_a_row():
     m = GpuMatcher(CHQ_TOPIC, CHQ_MODE_SPEC)
     m.bind_many(pb, poff, qb, qoff, d)
     m.commit()
+    from oracle import pyoracle as po
+    o = po.Oracle(po.TOPIC, po.SPEC, inplace=True)
+    assert o.bind_many(pb, poff, qb, qoff, d) == 0
     cap = 4_000_000
     # second call: fewer keys of another stream, plus keys the first call never saw (errors, long, empty)
     extra = [b".", b"..", b"", b"x" * 300, b"a.b.c.d.e.f.g.h.i.j"]
@@ -60,6 +64,12 @@ def test_static_scratch_entry_point_matches_the_allocating_one_twice_in_a_row():
         assert got[1] == want[1] and want[1] > 0
         for a, b in zip(want[2:], got[2:]):
             assert np.array_equal(a, b), "call %d" % call
+        # and against the CPU oracle: offsets, ids, durable flags, error flags
+        o_off, o_ids, o_dur, o_err = o.route_packed(blob, off, 4)
+        assert np.array_equal(got[2], o_off) and np.array_equal(got[3], o_ids), "call %d vs oracle" % call
+        # (a key longer than a shortstr is flagged by the product, err 2; the oracle takes any string)
+        short = np.diff(off.astype(np.int64)) <= 255
+        assert np.array_equal(got[4], o_dur) and np.array_equal((got[5] != 0)[short], (o_err != 0)[short]), "call %d vs oracle" % call
     # the slow merge path through the fixed arena (limits forced down), still identical
     m.debug_limits(1, 1)
     blob, off = w.keys(20_000, stream=42)
@@ -67,6 +77,8 @@ def test_static_scratch_entry_point_matches_the_allocating_one_twice_in_a_row():
     got = _run(torch, m, m.route_device_static, blob, off, cap)
     assert want[0] == 0 and got[0] == 0
     assert all(np.array_equal(a, b) for a, b in zip(want[2:], got[2:]))
+    o_off, o_ids, o_dur, _ = o.route_packed(blob, off, 4)
+    assert np.array_equal(got[2], o_off) and np.array_equal(got[3], o_ids) and np.array_equal(got[4], o_dur)
     m.debug_limits(0, 0)
 
 
@@ -78,7 +90,7 @@ def test_static_scratch_entry_point_refuses_what_does_not_fit():
     with pytest.raises(ChqError) as e:
         m.route_device_static(dummy, dummy, STATIC_MAX_KEYS + 1, dummy, dummy, 1, dummy, dummy, dummy, dummy)
     assert e.value.code == _lib.CHQ_E_ARG and "CHQ_STATIC_MAX_KEYS" in str(e.value)
-    m.bind("a.#.b", "q2")  # '#' inside a pattern: 128 word ids are kept per key, so far fewer keys fit
+    m.bind("a.#.b", "q2")  # '#' inside a pattern: 256 word ids are kept per key, so far fewer keys fit
     with pytest.raises(ChqError) as e:
         m.route_device_static(dummy, dummy, 5000, dummy, dummy, 1, dummy, dummy, dummy, dummy)
     assert e.value.code == _lib.CHQ_E_ARG and "CHQ_STATIC_MAX_WORDS" in str(e.value)
@@ -88,3 +100,18 @@ def test_static_scratch_entry_point_refuses_what_does_not_fit():
     blob, off = po.pack_keys(keys)
     st, total, offs, ids, dur, err = _run(torch, m, m.route_device_static, blob, off, 64)
     assert st == 0 and offs.tolist() == [0, 1, 3, 4, 4] and ids.tolist() == [0, 0, 1, 1]
+
+
+def test_static_scratch_entry_point_refuses_a_headers_table():
+    """x-match routing needs a per-batch descriptor arena the fixed array does not carry: the call must say so
+    instead of treating the header tables as routing keys and matching nothing"""
+    torch = pytest.importorskip("torch")
+    m = GpuMatcher(CHQ_HEADERS, CHQ_MODE_SPEC)
+    # arguments table: "x-match" = S "any", "k" = S "v"
+    args = b"\x07x-matchS\x00\x00\x00\x03any" + b"\x01kS\x00\x00\x00\x01v"
+    m.bind_args("", "q", False, args)
+    m.commit()
+    dummy = torch.zeros(64, dtype=torch.int64, device="cuda:0").data_ptr()
+    with pytest.raises(ChqError) as e:
+        m.route_device_static(dummy, dummy, 1, dummy, dummy, 1, dummy, dummy, dummy, dummy)
+    assert e.value.code == _lib.CHQ_E_ARG and "headers" in str(e.value)
