@@ -22,6 +22,7 @@
 #include "merge.cuh"
 #include "probe.cuh"
 #include "weave.cuh"
+#include "flat.cuh"
 
 #ifndef CHQ_MIN_CTAS
 #define CHQ_MIN_CTAS 8
@@ -30,7 +31,7 @@
 #define CHQ_PROBE_SORT 1
 #endif
 #ifndef CHQ_WRITE_CTAS
-#define CHQ_WRITE_CTAS 8
+#define CHQ_WRITE_CTAS 10
 #endif
 
 namespace chq {
@@ -311,7 +312,8 @@ namespace {
 
 constexpr uint32_t kMetaTiny = 1u << 13, kMetaDedup = 1u << 12;  // meta = k | class << 8 | flags
 constexpr uint32_t kMetaBig = 1u << 14;   // long result: k_write starts these first so that none is left for the end
-constexpr uint32_t kBigIds = 1024;
+constexpr uint32_t kMetaFlat = 1u << 15;  // one long list (<= kFlatMaxLong ids) + a short side, nothing shared: flat.cuh
+constexpr uint32_t kBigIds = 4096;
 
 }  // namespace
 
@@ -471,8 +473,9 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   if (m >= p.n) return;
   p.durable[m] = (flags & kAnyDurable) ? 1 : 0;
   p.cnt[m] = cnt;
+  const bool flat = cls == 0 && !tiny && !dedup && k >= 2 && k <= p.max_slots && mxlen <= (uint32_t)kFlatMaxLong;
   p.meta[m] = min(k, 255u) | ((uint32_t)cls << 8) | (dedup ? kMetaDedup : 0u) | (tiny ? kMetaTiny : 0u) |
-              ((cls == 3 || cnt >= kBigIds) ? kMetaBig : 0u);
+              ((cls == 3 || cnt >= kBigIds) ? kMetaBig : 0u) | (flat ? kMetaFlat : 0u);
   uint2* lists = p.mlist + (size_t)m * kRouteSlots;
   if (cls == 2) {
     lists[0] = make_uint2((uint32_t)scr, (uint32_t)(scr >> 32));
@@ -619,10 +622,12 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
 __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RouteParams p) {
   __shared__ WarpScratch ws_all[kRouteThreads / 32];
   __shared__ WeaveBuf wb_all[kRouteThreads / 32];
+  static_assert(sizeof(FlatBuf) <= sizeof(WeaveBuf::tile), "the group buffer of flat.cuh lives in the (idle) weave tile");
   const TableView& tv = p.tv;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpScratch& ws = ws_all[warp];
   WeaveBuf& wb = wb_all[warp];
+  FlatBuf& fb = *reinterpret_cast<FlatBuf*>(wb.tile);
   uint32_t phase = 0;
   weave_bar_init(wb, lane);
   const uint32_t n_chunks = (p.n + 31) / 32;
@@ -671,8 +676,20 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RoutePa
         }
         const bool big = (meta & kMetaBig) != 0;
         const bool sel = cnt > 0 && fits && !(meta & kMetaTiny) && (pass == 0 ? big : !big);
+        // the common kind, up to eight messages at a time: short ids placed by all lanes together, long lists streamed
+        const bool flat = sel && (meta & kMetaFlat);
+        for (unsigned fm = __ballot_sync(kFull, flat); fm;) {
+          unsigned gm = fm;
+          if (__popc(fm) > kFlatGroup) gm = fm & ((1u << __fns(fm, 0, kFlatGroup + 1)) - 1u);
+          fm &= ~gm;
+          flat_place(tv.qlist, p.mlist, p.ids, fb, gm, m, meta, cnt, pos, lane);
+          const int ng = __popc(gm);
+#pragma unroll 1
+          for (int g = 0; g < ng; ++g)
+            mask_stream(tv.qlist + fb.d[g][0].x, p.ids + fb.pos[g], fb.cnt[g], fb.cm[g], lane);
+        }
         // the list row of the next message is fetched while the current one is written
-        unsigned todo = __ballot_sync(kFull, sel);
+        unsigned todo = __ballot_sync(kFull, sel && !flat);
         auto row_of = [&](unsigned td) -> uint2 {
           if (td == 0 || lane >= kRouteSlots) return make_uint2(0u, 0u);
           return __ldg(p.mlist + (size_t)(base + __ffs(td) - 1) * kRouteSlots + lane);

@@ -21,12 +21,15 @@
 namespace chq {
 namespace {
 
-constexpr int kWeaveTile = 1024;                                     // long-list ids staged at a time
+#ifndef CHQ_WEAVE_TILE
+#define CHQ_WEAVE_TILE 576
+#endif
+constexpr int kWeaveTile = CHQ_WEAVE_TILE;                           // long-list ids staged at a time (multiple of 4)
 constexpr int kWeaveChunks = (kWeaveTile + kRouteSmall + 31 + 31) / 32 + 1;  // output chunks one tile can touch
 
 struct __align__(16) WeaveBuf {
   uint32_t tile[kWeaveTile + 4];   // +4: the bulk copy moves whole 16-byte units
-  uint32_t cmask[kWeaveChunks];    // per output chunk: the positions that take a short id
+  uint32_t cmask[kWeaveChunks < 32 ? 32 : kWeaveChunks];   // per output chunk: the positions that take a short id
   uint64_t bar;                    // mbarrier of the bulk copy
 };
 
@@ -186,7 +189,7 @@ __device__ __forceinline__ void warp_weave(const uint32_t* __restrict__ qlist, u
     const int u0 = ustart - (int)a0;   // start of the first chunk (may lie before the message)
     // positions before the message count as taken, like those of short ids: their lanes sit out
     wb.cmask[lane] = lane == 0 ? (1u << a0) - 1u : 0u;
-    if (lane < kWeaveChunks - 32) wb.cmask[32 + lane] = 0;
+    if (kWeaveChunks > 32 && lane < kWeaveChunks - 32) wb.cmask[32 + lane] = 0;
     if (bulk) {
       weave_bar_wait(wb, phase);
       phase ^= 1u;

@@ -9,7 +9,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CS = os.path.join(ROOT, "chanamq_b200", "csrc")
 regions = {}  # stripped source line -> region name
-for fn in ("chq_common.h", "probe.cuh", "merge.cuh", "kernels.cu"):
+for fn in ("chq_common.h", "probe.cuh", "merge.cuh", "weave.cuh", "flat.cuh", "kernels.cu"):
     region = fn
     for ln, line in enumerate(open(os.path.join(CS, fn)), 1):
         m = re.match(r"^(?:template.*\n)?(?:__device__|__global__|CHQ_HD).*?(\w+)\(", line)
