@@ -87,6 +87,7 @@ struct Workspace {
   DevBuf<uint32_t> scratch;
   DevBuf<uint32_t> cnt, meta;   // per message: id count, list count | class | flags (k_probe -> k_offsets, k_write)
   DevBuf<uint2> mlist;          // per message: its lists (offset, length), kRouteSlots each
+  DevBuf<uint32_t> rest;        // messages left to k_write_rest
   DevBuf<uint32_t> desc_k;      // headers exchange: matched lists per message (k_headers_match -> k_route)
   DevBuf<uint32_t> desc_start;
   DevBuf<uint8_t> desc_flags;
@@ -95,10 +96,10 @@ struct Workspace {
   size_t desc_want = 1u << 20;  // descriptor arena (grown after CHQ_E_SCRATCH)
   // optional per-kernel timing (chq_profile): events on the launching stream around each kernel
   static constexpr int kProfRing = 256;
-  cudaEvent_t ev[kProfRing][5] = {};  // start, after tokenize, after k_probe, after k_offsets, after k_write
+  cudaEvent_t ev[kProfRing][6] = {};  // start, after tokenize, k_probe, k_offsets, k_write, k_write_rest
   int prof_n = 0;
   void release() {
-    wid.release(); nwords.release(); state.release(); scratch.release(); cnt.release(); meta.release(); mlist.release();
+    wid.release(); nwords.release(); state.release(); scratch.release(); cnt.release(); meta.release(); mlist.release(); rest.release();
     desc_k.release(); desc_start.release(); desc_flags.release(); desc_lists.release();
     for (auto& e : ev) for (auto& x : e) if (x) { cudaEventDestroy(x); x = nullptr; }
     prof_n = 0;
@@ -258,6 +259,7 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   if ((rc = ws.cnt.ensure((size_t)n + 1))) return rc;
   if ((rc = ws.meta.ensure((size_t)n + 1))) return rc;
   if ((rc = ws.mlist.ensure((size_t)n * kRouteSlots + 1))) return rc;
+  if ((rc = ws.rest.ensure((size_t)n + 1))) return rc;
   CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + kStateHead) * sizeof(uint64_t), st));
   if (n == 0) {
     CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
@@ -269,7 +271,7 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   cudaEvent_t* pe = nullptr;
   if (t->profile && ws.prof_n < Workspace::kProfRing) {
     pe = ws.ev[ws.prof_n++];
-    for (int i = 0; i < 5; ++i)
+    for (int i = 0; i < 6; ++i)
       if (!pe[i]) CU(cudaEventCreate(&pe[i]));
     CU(cudaEventRecord(pe[0], st));
   }
@@ -297,6 +299,7 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   p.cnt = ws.cnt.p;
   p.meta = ws.meta.p;
   p.mlist = ws.mlist.p;
+  p.rest = ws.rest.p;
   p.scratch = ws.scratch.p;
   p.scratch_cap = ws.scratch.cap;
   p.max_slots = t->max_slots;
@@ -306,7 +309,7 @@ int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint
   { const char* dbg = getenv("CHQ_DEBUG"); p.debug = dbg ? (uint32_t)atoi(dbg) : 0u; }
 #endif
   CU(launch_route(p, t->n_sms, st, pe ? pe + 2 : nullptr));
-  if (pe) CU(cudaEventRecord(pe[4], st));
+  if (pe) CU(cudaEventRecord(pe[5], st));
   CU(launch_finish(p.ctrl, d_status, st));
   t->n_batches++;
   t->n_messages += n;
@@ -632,7 +635,8 @@ constexpr size_t kStaticOffState = 0;                                           
 constexpr size_t kStaticOffNwords = ((kStateHead + kStaticTiles) * 8 + 255) & ~size_t(255);      // u8[keys]
 constexpr size_t kStaticOffCnt = (kStaticOffNwords + kStaticMaxKeys + 255) & ~size_t(255);       // u32[keys]
 constexpr size_t kStaticOffMeta = kStaticOffCnt + (size_t)kStaticMaxKeys * 4;                    // u32[keys]
-constexpr size_t kStaticOffMlist = kStaticOffMeta + (size_t)kStaticMaxKeys * 4;                  // uint2[keys][kRouteSlots]
+constexpr size_t kStaticOffRest = kStaticOffMeta + (size_t)kStaticMaxKeys * 4;                   // u32[keys]
+constexpr size_t kStaticOffMlist = kStaticOffRest + (size_t)kStaticMaxKeys * 4;                  // uint2[keys][kRouteSlots]
 constexpr size_t kStaticOffWid = kStaticOffMlist + (size_t)kStaticMaxKeys * kRouteSlots * 8;     // u32[words]
 constexpr size_t kStaticOffArena = kStaticOffWid + (size_t)kStaticMaxWords * 4;                  // u32[arena]
 constexpr size_t kStaticBytes = kStaticOffArena + (size_t)kStaticArenaIds * 4;
@@ -709,6 +713,7 @@ int32_t chq_route_device_static(chq_table* t, const uint8_t* d_keys_blob, const 
   p.cnt = reinterpret_cast<uint32_t*>(base + kStaticOffCnt);
   p.meta = reinterpret_cast<uint32_t*>(base + kStaticOffMeta);
   p.mlist = reinterpret_cast<uint2*>(base + kStaticOffMlist);
+  p.rest = reinterpret_cast<uint32_t*>(base + kStaticOffRest);
   p.scratch = reinterpret_cast<uint32_t*>(base + kStaticOffArena);
   p.scratch_cap = kStaticArenaIds;
   p.max_slots = t->max_slots;
@@ -756,6 +761,7 @@ int32_t chq_merge_slices_device2(int32_t device, const uint32_t* d_slice_offsets
   if ((rc = ws.cnt.ensure((size_t)n + 1))) return rc;
   if ((rc = ws.meta.ensure((size_t)n + 1))) return rc;
   if ((rc = ws.mlist.ensure((size_t)n * kRouteSlots + 1))) return rc;
+  if ((rc = ws.rest.ensure((size_t)n + 1))) return rc;
   CU(cudaMemsetAsync(ws.state.p, 0, ((size_t)n_tiles + kStateHead) * sizeof(uint64_t), st));
   if (n == 0) {
     CU(cudaMemsetAsync(d_offsets, 0, sizeof(uint32_t), st));
@@ -781,6 +787,7 @@ int32_t chq_merge_slices_device2(int32_t device, const uint32_t* d_slice_offsets
   p.cnt = ws.cnt.p;
   p.meta = ws.meta.p;
   p.mlist = ws.mlist.p;
+  p.rest = ws.rest.p;
   p.scratch = ws.scratch.p;
   p.scratch_cap = ws.scratch.cap;
   p.max_slots = kRouteSlots;
@@ -822,20 +829,20 @@ int32_t chq_stats(const chq_table* t, char* json, uint32_t cap) {
   return (w < 0 || (uint32_t)w >= cap) ? fail(CHQ_E_ARG, "chq_stats: buffer too small") : CHQ_OK;
 }
 
-static int32_t profile_collect(chq_table* t, int32_t enable, double ms[4], uint32_t* launches, const char* who) {
+static int32_t profile_collect(chq_table* t, int32_t enable, double ms[5], uint32_t* launches, const char* who) {
   if (!t) return fail(CHQ_E_ARG, std::string(who) + ": bad argument");
   if (t->host_only) return fail(CHQ_E_CUDA, std::string(who) + ": host-only table");
   int rc = set_device(t);
   if (rc) return rc;
   CU(cudaDeviceSynchronize());
   uint32_t cnt = 0;
-  for (int k = 0; k < 4; ++k) ms[k] = 0;
+  for (int k = 0; k < 5; ++k) ms[k] = 0;
   Workspace* all[CHQ_SLOTS + 1];
   for (int i = 0; i < CHQ_SLOTS; ++i) all[i] = &t->slots[i].ws;
   all[CHQ_SLOTS] = &t->dev_ws;
   for (Workspace* ws : all) {
     for (int i = 0; i < ws->prof_n; ++i) {
-      for (int k = 0; k < 4; ++k) {
+      for (int k = 0; k < 5; ++k) {
         float a = 0;
         CU(cudaEventElapsedTime(&a, ws->ev[i][k], ws->ev[i][k + 1]));
         ms[k] += a;
@@ -850,11 +857,11 @@ static int32_t profile_collect(chq_table* t, int32_t enable, double ms[4], uint3
 }
 
 int32_t chq_profile(chq_table* t, int32_t enable, double* tokenize_ms, double* route_ms, uint32_t* launches) {
-  double ms[4];
+  double ms[5];
   int rc = profile_collect(t, enable, ms, launches, "chq_profile");
   if (rc) return rc;
   if (tokenize_ms) *tokenize_ms = ms[0];
-  if (route_ms) *route_ms = ms[1] + ms[2] + ms[3];
+  if (route_ms) *route_ms = ms[1] + ms[2] + ms[3] + ms[4];
   return CHQ_OK;
 }
 

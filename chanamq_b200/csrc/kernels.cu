@@ -30,8 +30,11 @@
 #ifndef CHQ_PROBE_SORT
 #define CHQ_PROBE_SORT 1
 #endif
+#ifndef CHQ_EXP
+#define CHQ_EXP 0   // timing experiments only (results are wrong): 1 no stream, 2 no placement, 4 no tiny messages,
+#endif              // 8 no flat messages at all, 16 no k_write_rest launch
 #ifndef CHQ_WRITE_CTAS
-#define CHQ_WRITE_CTAS 10
+#define CHQ_WRITE_CTAS 8
 #endif
 
 namespace chq {
@@ -427,7 +430,10 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   else if (k <= 1) cnt = ub;
   else if (k > p.max_slots) cls = 2;
   // one long list + at most max_small other ids: k_write's staged weave (weave.cuh); more: warp_union_long
-  else if (ub - mxlen > p.max_small || ub >= (1u << 30)) { cls = 3; cnt = ub; }  // dedup: counted below
+  // (nothing shared between the lists: the flat path of k_write takes a much longer short side)
+  else if (ub - mxlen > ((dedup || mxlen > (uint32_t)kFlatMaxLong || p.max_small != (uint32_t)kRouteSmall) ? p.max_small
+                                                                                                             : (uint32_t)kFlatMaxShort) ||
+           ub >= (1u << 30)) { cls = 3; cnt = ub; }  // dedup: counted below
   else if (dedup) cls = 1;
   else cnt = ub;
 
@@ -473,7 +479,8 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   if (m >= p.n) return;
   p.durable[m] = (flags & kAnyDurable) ? 1 : 0;
   p.cnt[m] = cnt;
-  const bool flat = cls == 0 && !tiny && !dedup && k >= 2 && k <= p.max_slots && mxlen <= (uint32_t)kFlatMaxLong;
+  // (a single list is the same thing with an empty short side)
+  const bool flat = cls == 0 && !tiny && (!dedup || k == 1) && k >= 1 && k <= p.max_slots && mxlen <= (uint32_t)kFlatMaxLong;
   p.meta[m] = min(k, 255u) | ((uint32_t)cls << 8) | (dedup ? kMetaDedup : 0u) | (tiny ? kMetaTiny : 0u) |
               ((cls == 3 || cnt >= kBigIds) ? kMetaBig : 0u) | (flat ? kMetaFlat : 0u);
   uint2* lists = p.mlist + (size_t)m * kRouteSlots;
@@ -619,91 +626,133 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
   }
 }
 
+// k_write: the two kinds of message that make up almost all of a batch — tiny results (their own lane gathers, sorts
+// and writes) and one long list plus a short side (flat.cuh).  Persistent warps take 32 consecutive messages per grab;
+// the grab after next and the next chunk's words are fetched while the current chunk is written (a grab is an atomic
+// plus three dependent loads: unhidden, that chain was a third of the kernel).  Everything else (unions of several
+// long lists, de-duplicating merges, slow-path results parked in scratch, the headers exchange's many small lists)
+// is put on a work list for k_write_rest, which has its own register budget.
 __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RouteParams p) {
-  __shared__ WarpScratch ws_all[kRouteThreads / 32];
-  __shared__ WeaveBuf wb_all[kRouteThreads / 32];
-  static_assert(sizeof(FlatBuf) <= sizeof(WeaveBuf::tile), "the group buffer of flat.cuh lives in the (idle) weave tile");
-  const TableView& tv = p.tv;
+  __shared__ FlatBuf fb_all[kRouteThreads / 32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  WarpScratch& ws = ws_all[warp];
-  WeaveBuf& wb = wb_all[warp];
-  FlatBuf& fb = *reinterpret_cast<FlatBuf*>(wb.tile);
-  uint32_t phase = 0;
-  weave_bar_init(wb, lane);
-  const uint32_t n_chunks = (p.n + 31) / 32;
+  FlatBuf& fb = fb_all[warp];
   if (*p.total > 0xFFFFFFFFull) return;  // offsets saturated: the launch reports CHQ_E_OVERFLOW
 #ifdef CHQ_DEBUG_SWITCHES
   if (p.debug & 1u) return;
 #endif
+  // (through an asm move, so that the compiler keeps the pointer in one register pair and forms list addresses with
+  // one multiply-add: left alone it re-derives them from the kernel parameters, five instructions per load)
+  const uint32_t* ql;
+  asm("mov.b64 %0, %1;" : "=l"(ql) : "l"(p.tv.qlist));
+  // Work is handed out in units of eight messages: four units (one lane per message) per grab for most of the batch,
+  // two and then one towards its end, where a whole 32-message chunk per warp would leave the other warps waiting for
+  // the last ones (a chunk takes about a seventh of the kernel's run time).
+  const uint32_t n_units = (p.n + 7) / 8;
+  const uint32_t tail2 = n_units - n_units / 8, tail1 = n_units - n_units / 24;
+  uint32_t u = 0, take = 4;
+  auto grab = [&]() {
+    uint32_t r = 0;
+    if (lane == 0) r = atomicAdd(p.ctrl + kCtrlChunk, take);
+    u = __shfl_sync(kFull, r, 0);
+  };
+  uint32_t meta, cnt, pos, m;
+  auto fetch = [&]() {
+    m = u * 8 + lane;
+    meta = cnt = pos = 0;
+    if ((uint32_t)lane < 8 * take && m < p.n) { meta = CHQ_LD_ONCE(p.meta + m); cnt = CHQ_LD_ONCE(p.cnt + m); pos = p.offsets[m]; }
+  };
+  for (grab(); u < n_units; grab()) {
+    fetch();
+    take = u >= tail1 ? 1u : (u >= tail2 ? 2u : 4u);   // size of the NEXT grab
+    const bool fits = (uint64_t)pos + cnt <= p.ids_cap;  // else CHQ_E_OVERFLOW: nothing is written past ids_cap
+    const bool live = cnt > 0 && fits;
+    if (!(CHQ_EXP & 4) && live && (meta & kMetaTiny)) {
+      const uint2* lists = p.mlist + (size_t)m * kRouteSlots;
+      auto off = [&](uint32_t j) { return __ldg(lists + j).x; };
+      auto len = [&](uint32_t j) { return __ldg(lists + j).y; };
+      tiny_union(ql, meta & 0xFF, off, len, p.ids + pos);
+    }
+    __syncwarp();
+    {  // what this kernel does not do goes on k_write_rest's list: long results from the front, the others from the back
+      const bool other = live && !(meta & (kMetaTiny | kMetaFlat));
+      const unsigned om = __ballot_sync(kFull, other);
+      if (om) {
+        const bool big = (meta & kMetaBig) != 0;
+        const unsigned bm = __ballot_sync(kFull, other && big), sm = om & ~bm;
+        uint32_t b0 = 0, s0 = 0;
+        if (lane == 0) {
+          if (bm) b0 = atomicAdd(p.ctrl + kCtrlRestBig, (uint32_t)__popc(bm));
+          if (sm) s0 = atomicAdd(p.ctrl + kCtrlRest, (uint32_t)__popc(sm));
+        }
+        b0 = __shfl_sync(kFull, b0, 0);
+        s0 = __shfl_sync(kFull, s0, 0);
+        const uint32_t ltm = (1u << lane) - 1u;
+        if (other) p.rest[big ? b0 + __popc(bm & ltm) : p.n - 1u - (s0 + __popc(sm & ltm))] = m;
+      }
+    }
+    // up to eight messages at a time: short ids placed by all lanes together, long lists streamed
+    for (unsigned fm = (CHQ_EXP & 8) ? 0u : __ballot_sync(kFull, live && (meta & kMetaFlat)); fm;) {
+      unsigned gm = fm;
+      if (__popc(fm) > kFlatGroup) gm = fm & ((1u << __fns(fm, 0, kFlatGroup + 1)) - 1u);
+      fm &= ~gm;
+      flat_place(ql, p.mlist, p.ids, fb, gm, m, meta, cnt, pos, lane);
+      const int ng = (CHQ_EXP & 1) ? 0 : __popc(gm);
+#pragma unroll 1
+      for (int gi = 0; gi < ng; ++gi)
+        mask_stream(ql + fb.d[gi][0].x, p.ids + fb.pos[gi], fb.cnt[gi], fb.cm[gi], lane);
+    }
+  }
+}
+
+// The messages k_write left out, from its work list: those with long results first (so that the longest jobs start
+// first instead of being met by chance near the end), eight messages per grab, one per warp trip.
+__global__ void __launch_bounds__(kRouteThreads, 8) k_write_rest(RouteParams p) {
+  __shared__ WarpScratch ws_all[kRouteThreads / 32];
+  __shared__ WeaveBuf wb_all[kRouteThreads / 32];
+  const TableView& tv = p.tv;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t n_big = p.ctrl[kCtrlRestBig], n_all = n_big + p.ctrl[kCtrlRest];
+  if (n_all == 0 || *p.total > 0xFFFFFFFFull) return;
+#ifdef CHQ_DEBUG_SWITCHES
+  if (p.debug & 1u) return;
+#endif
+  WarpScratch& ws = ws_all[warp];
+  WeaveBuf& wb = wb_all[warp];
+  uint32_t phase = 0;
+  weave_bar_init(wb, lane);
   const WriteCtx wc{p.desc_lists, tv.qlist, p.mlist, p.scratch, p.ids, p.ids_cap,
                     !p.slice_offsets && (reinterpret_cast<uintptr_t>(tv.qlist) & 15u) == 0};
-  // Two passes over the batch, 32 consecutive messages per sub-chunk.  Pass 0 sweeps the meta words (four
-  // sub-chunks per grab) and does only the few messages with long results, so that the longest jobs start
-  // first instead of being met by chance near the end of the kernel; pass 1 does everything else.
-#pragma unroll 1
-  for (int pass = 0; pass < 2; ++pass) {
-    const uint32_t span = pass == 0 ? 4u : 1u;
-    for (;;) {
-      CHQ_CLK_T0();
-      uint32_t g = 0;
-      if (lane == 0) g = atomicAdd(p.ctrl + (pass == 0 ? kCtrlBig : kCtrlChunk), 1u);
-      g = __shfl_sync(kFull, g, 0);
-      if ((uint64_t)g * span >= n_chunks) break;
-#pragma unroll 1
-      for (uint32_t q = 0; q < span; ++q) {
-        const uint32_t base = (g * span + q) * 32;
-        if (base >= p.n) break;
-        const uint32_t m = base + lane;
-        uint32_t cnt = 0, meta = 0, pos = 0;
-        if (m < p.n) {
-          meta = p.meta[m];
-          if (pass == 1 || (meta & kMetaBig)) { cnt = p.cnt[m]; pos = p.offsets[m]; }
-        }
-        const bool fits = (uint64_t)pos + cnt <= p.ids_cap;  // else CHQ_E_OVERFLOW: nothing is written past ids_cap
-        CHQ_CLK_ADD(pass == 0 ? 0 : 7, 0, 0);
-        if (pass == 1) {
-          CHQ_CLK_T0();
-          if ((meta & kMetaTiny) && cnt > 0 && fits) {  // tiny messages: their own lane gathers, sorts and writes
-            const uint2* lists = p.mlist + (size_t)m * kRouteSlots;
-            auto off = [&](uint32_t j) { return __ldg(lists + j).x; };
-            auto len = [&](uint32_t j) { return __ldg(lists + j).y; };
-            tiny_union(tv.qlist, meta & 0xFF, off, len, p.ids + pos);
-          }
-          __syncwarp();
-          const uint32_t n_tiny = __popc(__ballot_sync(kFull, (meta & kMetaTiny) && cnt > 0));
-          (void)n_tiny;
-          CHQ_CLK_ADD(1, n_tiny, 0);
-        }
-        const bool big = (meta & kMetaBig) != 0;
-        const bool sel = cnt > 0 && fits && !(meta & kMetaTiny) && (pass == 0 ? big : !big);
-        // the common kind, up to eight messages at a time: short ids placed by all lanes together, long lists streamed
-        const bool flat = sel && (meta & kMetaFlat);
-        for (unsigned fm = __ballot_sync(kFull, flat); fm;) {
-          unsigned gm = fm;
-          if (__popc(fm) > kFlatGroup) gm = fm & ((1u << __fns(fm, 0, kFlatGroup + 1)) - 1u);
-          fm &= ~gm;
-          flat_place(tv.qlist, p.mlist, p.ids, fb, gm, m, meta, cnt, pos, lane);
-          const int ng = __popc(gm);
-#pragma unroll 1
-          for (int g = 0; g < ng; ++g)
-            mask_stream(tv.qlist + fb.d[g][0].x, p.ids + fb.pos[g], fb.cnt[g], fb.cm[g], lane);
-        }
-        // the list row of the next message is fetched while the current one is written
-        unsigned todo = __ballot_sync(kFull, sel && !flat);
-        auto row_of = [&](unsigned td) -> uint2 {
-          if (td == 0 || lane >= kRouteSlots) return make_uint2(0u, 0u);
-          return __ldg(p.mlist + (size_t)(base + __ffs(td) - 1) * kRouteSlots + lane);
-        };
-        uint2 row = row_of(todo);
-        while (todo) {
-          const int src = __ffs(todo) - 1;
-          todo &= todo - 1;
-          const uint2 mine = row;
-          row = row_of(todo);
-          write_message(wc, ws, wb, phase, mine.x, mine.y, __shfl_sync(kFull, cnt, src), __shfl_sync(kFull, meta, src),
-                        __shfl_sync(kFull, pos, src), lane);
-        }
-      }
+  constexpr uint32_t kPerGrab = 8;
+  for (;;) {
+    CHQ_CLK_T0();
+    uint32_t i0 = 0;
+    if (lane == 0) i0 = atomicAdd(p.ctrl + kCtrlRestNext, kPerGrab);
+    i0 = __shfl_sync(kFull, i0, 0);
+    if (i0 >= n_all) break;
+    // lane j < 8: item i0 + j of the list (long results sit at the front of p.rest, the others at its back)
+    const uint32_t i = i0 + lane;
+    uint32_t m = 0, cnt = 0, meta = 0, pos = 0;
+    if ((uint32_t)lane < kPerGrab && i < n_all) {
+      m = p.rest[i < n_big ? i : p.n - 1u - (i - n_big)];
+      meta = p.meta[m]; cnt = p.cnt[m]; pos = p.offsets[m];
+    }
+    CHQ_CLK_ADD(7, 0, 0);
+    // the list row of the next message is fetched while the current one is written
+    unsigned todo = __ballot_sync(kFull, cnt > 0);
+    auto row_of = [&](unsigned td) -> uint2 {
+      if (td == 0) return make_uint2(0u, 0u);
+      const uint32_t mm = __shfl_sync(kFull, m, __ffs(td) - 1);
+      if (lane >= kRouteSlots) return make_uint2(0u, 0u);
+      return __ldg(p.mlist + (size_t)mm * kRouteSlots + lane);
+    };
+    uint2 row = row_of(todo);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const uint2 mine = row;
+      row = row_of(todo);
+      write_message(wc, ws, wb, phase, mine.x, mine.y, __shfl_sync(kFull, cnt, src), __shfl_sync(kFull, meta, src),
+                    __shfl_sync(kFull, pos, src), lane);
     }
   }
 }
@@ -762,11 +811,16 @@ cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st, cudaE
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
+  static int occ_rest_by_dev[64] = {};
   int& occ = occ_by_dev[dev & 63];
-  if (occ == 0) {  // once per device: size the persistent grid of the write kernel
+  int& occ_rest = occ_rest_by_dev[dev & 63];
+  if (occ == 0) {  // once per device: size the persistent grids of the write kernels
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_write, kRouteThreads, 0);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_rest, k_write_rest, kRouteThreads, 0);
+    if (e != cudaSuccess) return e;
+    if (occ_rest < 1) occ_rest = 1;
   }
   k_probe<<<(p.n + kRouteThreads - 1) / kRouteThreads, kRouteThreads, sizeof(RouteSmem), st>>>(p);
   if (between && (e = cudaEventRecord(between[0], st)) != cudaSuccess) return e;
@@ -774,7 +828,10 @@ cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st, cudaE
   if (between && (e = cudaEventRecord(between[1], st)) != cudaSuccess) return e;
   const uint64_t want = (uint64_t)n_sms * occ, chunks = (p.n + 31) / 32;
   k_write<<<(uint32_t)(chunks < want ? chunks : want), kRouteThreads, 0, st>>>(p);
-  g_launches += 3;
+  if (between && (e = cudaEventRecord(between[2], st)) != cudaSuccess) return e;
+  const uint64_t want_rest = (uint64_t)n_sms * occ_rest;   // (its warps pull work from the list; usually it is short)
+  if (!(CHQ_EXP & 16)) k_write_rest<<<(uint32_t)(chunks < want_rest ? chunks : want_rest), kRouteThreads, 0, st>>>(p);
+  g_launches += 4;
   return cudaGetLastError();
 }
 

@@ -18,7 +18,9 @@ constexpr int kRouteSmall = CHQ_ROUTE_SMALL;     // ids (all lists but the longe
 // control words (device): zeroed before every launch
 constexpr int kCtrlTile = 0 /* scan tile counter */, kCtrlStatus = 1, kCtrlScratchLo = 2 /* u64 bump pointer */,
               kCtrlChunk = 4 /* write-kernel work counter */, kCtrlDescBump = 5 /* headers descriptor arena */,
-              kCtrlBig = 6 /* write-kernel counter of its first pass (big messages) */, kCtrlWords = 8;
+              kCtrlRestBig = 6 /* messages k_write leaves to k_write_rest: long results (done first) */,
+              kCtrlRest = 7 /* ... and the others */, kCtrlRestNext = 8 /* k_write_rest's work counter */,
+              kCtrlWords = 16;
 constexpr int kRouteScanTile = 1024;  // counts per tile of the offsets scan
 constexpr int kStateHead = kCtrlWords / 2;  // the control words take the first kStateHead u64 of the state array
 inline uint32_t route_scan_tiles(uint32_t n) { return (n + kRouteScanTile - 1) / kRouteScanTile; }
@@ -38,6 +40,8 @@ struct RouteParams {
   uint32_t* cnt;             // [n] scratch: ids per message (k_probe -> k_offsets, k_write)
   uint32_t* meta;            // [n] scratch: lists | class << 8 | flags
   uint2* mlist;              // [n][kRouteSlots] scratch: the message's lists (offset, length)
+  uint32_t* rest;            // [n] scratch: the messages k_write leaves to k_write_rest (long results from the front,
+                             //     the others from the back)
   uint64_t* tile_state;      // [n_tiles] scratch of the offsets scan, zeroed before launch
   uint32_t* ctrl;            // [kCtrlWords] scratch, zeroed before launch
   uint32_t* scratch;         // slow-path arena
@@ -66,7 +70,7 @@ void note_launches(int n);
 cudaError_t launch_headers_match(const uint8_t* blob, const uint32_t* off, const uint32_t* hlen, uint32_t n, const TableView& tv,
                                  uint32_t* desc_k, uint32_t* desc_start, uint8_t* desc_flags, uint2* desc_lists, uint32_t arena_cap,
                                  uint32_t* arena_used, uint32_t* status_word, uint8_t* err, cudaStream_t st);
-// between: optional two events, recorded after k_probe and after k_offsets (per-kernel timing)
+// between: optional three events, recorded after k_probe, k_offsets and k_write (per-kernel timing)
 cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st, cudaEvent_t* between = nullptr);
 cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t st);
 unsigned long long kernel_launches();

@@ -11,6 +11,25 @@
 #include "kernels.h"
 #include "probe.cuh"
 
+// Queue ids are written once and not read again by this launch group: streaming stores (evict-first), so that the
+// 0.4 GB a batch writes passes through L2 without pushing the compiled table out of it.
+#ifndef CHQ_STREAM_STORES
+#define CHQ_STREAM_STORES 1
+#endif
+#if CHQ_STREAM_STORES
+#define CHQ_ST_OUT(ptr, val) __stcs((ptr), (val))
+#else
+#define CHQ_ST_OUT(ptr, val) (*(ptr) = (val))
+#endif
+#ifndef CHQ_STREAM_LOADS
+#define CHQ_STREAM_LOADS 0
+#endif
+#if CHQ_STREAM_LOADS   // per-message words k_probe left for k_write: read once
+#define CHQ_LD_ONCE(ptr) __ldcs(ptr)
+#else
+#define CHQ_LD_ONCE(ptr) (*(ptr))
+#endif
+
 namespace chq {
 namespace {
 
@@ -135,7 +154,7 @@ __device__ __forceinline__ uint32_t tiny_union(const uint32_t* __restrict__ qlis
   for (int s = 0; s < kTinyIds; ++s) {
     const bool keep = v[s] != kNone && (s == 0 || v[s] != v[s - 1]);
     if (keep) {
-      if (out) out[n] = v[s];
+      if (out) CHQ_ST_OUT(out + n, v[s]);
       ++n;
     }
   }

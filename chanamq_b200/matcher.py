@@ -176,9 +176,9 @@ class GpuMatcher:
 
     def profile_kernels(self, enable):
         """-> ({kernel: ms summed since the last call}, batches); then switch recording on/off"""
-        ms, n = (C.c_double * 4)(), C.c_uint32()
+        ms, n = (C.c_double * 5)(), C.c_uint32()
         check(self.L.chq_profile_kernels(self.h, int(enable), ms, C.byref(n)))
-        return dict(zip(("k_tokenize", "k_probe", "k_offsets", "k_write"), list(ms))), n.value
+        return dict(zip(("k_tokenize", "k_probe", "k_offsets", "k_write", "k_write_rest"), list(ms))), n.value
 
     def debug_limits(self, max_slots=0, max_small=0):
         check(self.L.chq_debug_limits(self.h, max_slots, max_small))

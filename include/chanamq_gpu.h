@@ -290,11 +290,12 @@ int32_t chq_host_free(void* p);
  * ids, device bytes of the table */
 int32_t chq_stats(const chq_table* t, char* json, uint32_t cap);
 /* Per-kernel device time, measured with CUDA events recorded on the launching stream around k_tokenize
- * and the route kernels (k_probe + k_offsets + k_write).  The call synchronises the device, returns the
+ * and the route kernels (k_probe + k_offsets + k_write + k_write_rest).  The call synchronises the device, returns the
  * sums (ms) and the number of batches since the last call (at most 256 are kept), then switches recording
  * on or off. */
 int32_t chq_profile(chq_table* t, int32_t enable, double* tokenize_ms, double* route_ms, uint32_t* launches);
-/* The same, one sum per kernel: kernel_ms[0..3] = k_tokenize (or k_headers_match), k_probe, k_offsets, k_write. */
+/* The same, one sum per kernel: kernel_ms[0..4] = k_tokenize (or k_headers_match), k_probe, k_offsets, k_write,
+ * k_write_rest. */
 int32_t chq_profile_kernels(chq_table* t, int32_t enable, double* kernel_ms, uint32_t* launches);
 /* how many of this library's kernels have been launched by this process (all tables) */
 uint64_t chq_kernel_launches(void);

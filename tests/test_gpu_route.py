@@ -180,18 +180,20 @@ def test_config2_topic_100k_bindings(mode, hash_tail, nq):
     assert st["bindings"] > 99_000 and st["wstride"] == 8
 
 
-def test_full_size_1m_bindings_properties_and_sample():
-    """configs[3] table (1 M bindings) at one full batch of 2^20 keys: CSR invariants over the whole
-    result, idempotence, and exact equality with the oracle on a 20 k-key sample"""
-    w, m, o = _load_workload(4, 1_000_000, 1_000_000, CHQ_MODE_SPEC, True)
+@pytest.mark.parametrize("mode", [CHQ_MODE_COMPAT, CHQ_MODE_SPEC])
+def test_full_size_1m_bindings_properties_and_sample(mode):
+    """configs[3] table (1 M bindings) at one full batch of 2^20 keys, in the benchmark's own mode (COMPAT) and with
+    the '#' wildcard: CSR invariants over the whole result, idempotence, and exact equality with the oracle on a
+    120 k-key sample"""
+    w, m, o = _load_workload(4, 1_000_000, 1_000_000, mode, True)
     blob, off = w.keys(1 << 20, stream=3)
     r1 = m.route_packed(blob, off)
     check_csr_invariants(r1, m.n_queues())
     r2 = m.route_packed(blob, off)
     assert all(np.array_equal(a, b) for a, b in zip(r1, r2))
-    n_s = 20_000
+    n_s = 120_000
     sblob, soff = blob[: off[n_s]], off[: n_s + 1]
-    rs = assert_same_routing(m, o, sblob, soff, threads=4)
+    rs = assert_same_routing(m, o, sblob, soff, threads=8)
     assert np.array_equal(rs.offsets, r1.offsets[: n_s + 1]) and np.array_equal(rs.queue_ids, r1.queue_ids[: rs.offsets[-1]])
     # linearity: routing the two halves separately concatenates to the whole
     half = 1 << 19
