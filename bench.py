@@ -283,6 +283,8 @@ def run_ours(a, rank, world, local_rank):
     h2d = int(np.mean([hb.numel() + ho.numel() * 4 for hb, ho in host]))
     d2h = int((n + 1) * 4 + 2 * n + 16 + ids_per_batch * 4)
 
+    slices = run_binding_slices(a, rank, world, local_rank, w, binds, mbar, dist, barrier) if world > 1 else None
+
     t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if dist:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -334,6 +336,8 @@ def run_ours(a, rank, world, local_rank):
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                          "tokenize_ms": tok_ms / max(1, prof_n), "kernel_share_of_step": route_ms / dev_ms if world == 1 else None},
         }
+        if slices is not None:
+            out["binding_slices"] = slices
         if world == 1 and not a.no_cpu_baseline:
             rate, per_step, cbuild, cm, _, want = cpu_route_rate(a, w, binds, a.cpu_sample, 1, 1, 0, stream0=0)
             # parity of the timed path on the timed configuration: the oracle has just routed the first cpu_sample keys
@@ -353,11 +357,101 @@ def run_ours(a, rank, world, local_rank):
                                              "reference, ExchangeEntity.scala:107), %.1f s; trie build %.1f s not timed; "
                                              "C++ restatement of TrieMatcher (no JVM here)" % (a.cpu_sample, per_step, cbuild)}
         print(json.dumps(out))
+        if (out.get("binding_slices") or {}).get("parity", {}).get("equal") is False:
+            raise SystemExit("bench.py: the binding-slice result differs from the oracle's")
         if out.get("parity", {}).get("equal") is False:
             raise SystemExit("bench.py: the product's result differs from the oracle's on the benchmarked configuration")
     if dist:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_binding_slices(a, rank, world, local_rank, w, binds, mbar, dist, barrier):
+    """BASELINE.json configs[3] as written: binding i on GPU i mod G, every GPU routes ALL keys of a batch against its
+    slice, the slices' results meet over NVLink (NCCL all-gather of the small arrays + peer reads of the ids) and rank g
+    ends with the finished result of messages [g n / G, (g+1) n / G) — one chq_shard_route_device call per rank per batch.
+    A step = one batch of n keys for the WHOLE job (the same keys on every rank)."""
+    import torch
+
+    from chanamq_b200 import CHQ_MODE_COMPAT, CHQ_MODE_SPEC, CHQ_TOPIC
+    from chanamq_b200.sharded import ShardedExchange
+
+    dev = torch.device("cuda", local_rank)
+    n = a.batch
+    box = [ShardedExchange.unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    t0 = time.perf_counter()
+    ex = ShardedExchange(box[0], rank, world, local_rank, CHQ_TOPIC, CHQ_MODE_COMPAT if a.mode == "compat" else CHQ_MODE_SPEC)
+    ex.bind_many(*binds)
+    ex.commit()
+    mb = torch.tensor([mbar], dtype=torch.float64, device=dev)   # (every rank measured it on its own key batches)
+    dist.all_reduce(mb, op=dist.ReduceOp.MAX)
+    mbar = float(mb[0])
+    slice_cap = int(n * (mbar / world * 1.3 + 8)) + 4096
+    pull_cap = int(n / world * (mbar / world * 1.5 + 8)) + 4096
+    ids_cap = int(n / world * (mbar * 1.5 + 16)) + 4096
+    ex.reserve(n, slice_cap, pull_cap)
+    build_s = time.perf_counter() - t0
+    keys = []
+    for b in range(N_BATCHES):  # the same batches on every rank
+        blob, off = w.keys(n, stream=5000 + b)
+        keys.append((torch.from_numpy(blob.copy()).to(dev), torch.from_numpy(off.view(np.int32).copy()).to(dev), blob if b == 0 else None,
+                     off if b == 0 else None))
+    nn_max = n // world + 2
+    d_offsets = torch.empty(nn_max + 1, dtype=torch.int32, device=dev)
+    d_ids = torch.empty(ids_cap, dtype=torch.int32, device=dev)
+    d_dur = torch.empty(nn_max, dtype=torch.uint8, device=dev)
+    d_err = torch.empty(nn_max, dtype=torch.uint8, device=dev)
+    d_tot = torch.zeros(2, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step(i):
+        db, do, _, _ = keys[i % N_BATCHES]
+        return ex.route_device(db.data_ptr(), do.data_ptr(), n, d_offsets.data_ptr(), d_ids.data_ptr(), ids_cap, d_dur.data_ptr(),
+                               d_err.data_ptr(), d_tot.data_ptr(), d_tot.data_ptr() + 8, stream)
+
+    for i in range(a.warmup):
+        step(i)
+    barrier()
+    ex.stage_ms(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(a.steps):
+        step(a.warmup + i)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    stages, stage_n = ex.stage_ms(False)
+    status = int(d_tot[1].item()) & 0xFFFFFFFF
+    # parity: batch 0 once more; rank 0 compares the head of its range with the oracle over the WHOLE table
+    m0, m1 = step(0)
+    torch.cuda.synchronize()
+    parity = None
+    if rank == 0:
+        from oracle import pyoracle as po
+
+        o = po.Oracle(po.TOPIC, po.COMPAT if a.mode == "compat" else po.SPEC, inplace=True)
+        assert o.bind_many(*binds) == 0
+        ns = min(20_000, m1 - m0)
+        blob, off = keys[0][2], keys[0][3]
+        w_off, w_ids, w_dur, _ = o.route_packed(blob[: off[ns]], off[: ns + 1], os.cpu_count() or 1)
+        g_off = d_offsets[: ns + 1].cpu().numpy().view(np.uint32)
+        equal = bool(np.array_equal(g_off, w_off) and np.array_equal(d_ids[: int(w_off[-1])].cpu().numpy().view(np.uint32), w_ids) and
+                     np.array_equal(d_dur[:ns].cpu().numpy(), w_dur))
+        parity = {"checked_keys": int(ns), "checked_ids": int(len(w_ids)), "equal": equal,
+                  "against": "CPU oracle over the whole table, head of rank 0's message range of batch 0"}
+    t = torch.tensor([ms, float(status != 0)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    ex.close()
+    return {"value": n * a.steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / a.steps, "status_ok": float(t[1]) == 0.0,
+            "what": "bindings sliced i mod G; every GPU routes all %d keys of a step against its slice; ncclAllGather of the slices' "
+                    "offsets and durable flags; each GPU pulls the ids of its own n/G messages from the peers' buffers over NVLink "
+                    "and merges them (chq_shard_route_device)" % n,
+            "nccl_bytes_received_per_rank_per_step": int(world * ((n + 2) * 4 + n)),
+            "peer_bytes_pulled_per_rank_per_step": int(4 * mbar * n / world * (world - 1) / world),
+            "setup_s": build_s, "parity": parity,
+            "stage_ms_rank0": {k: v / max(1, stage_n) for k, v in stages.items()}}
 
 
 def main():

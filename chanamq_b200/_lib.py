@@ -64,6 +64,17 @@ def load_library():
         "chq_declare_queues": (i32, [vp, vp, vp, u32]),
         "chq_merge_slices_device": (i32, [i32, vp, vp, u64, vp, u32, u32, vp, vp, u64, vp, vp, vp, vp]),
         "chq_merge_slices_device2": (i32, [i32, vp, vp, u64, vp, u32, u32, vp, vp, u64, vp, vp, vp, u32, vp]),
+        "chq_shard_unique_id": (i32, [vp]),
+        "chq_shard_create": (i32, [C.POINTER(vp), vp, i32, i32, i32, i32, i32]),
+        "chq_shard_destroy": (i32, [vp]),
+        "chq_shard_table": (vp, [vp]),
+        "chq_shard_bind_many": (i32, [vp, vp, vp, vp, vp, vp, u32, u32]),
+        "chq_shard_commit": (i32, [vp]),
+        "chq_shard_is_disjoint": (i32, [vp]),
+        "chq_shard_reserve": (i32, [vp, u32, u64, u64]),
+        "chq_shard_route_device": (i32, [vp, vp, vp, u32, vp, vp, u64, vp, vp, vp, vp, C.POINTER(u32), C.POINTER(u32), vp]),
+        "chq_shard_stage_ms": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(u32)]),
+        "chq_shard_last_error": (C.c_char_p, []),
         "chq_decode": (i32, [vp, u64, vp, u32, vp, u64, C.POINTER(u64), vp, vp, vp]),
         "chq_decode_device": (i32, [vp, u64, vp, u32, vp, u64, vp, vp, vp, vp, vp, vp]),
         "chq_publish_keys_device": (i32, [vp, vp, u64, vp, vp, vp, vp, vp]),

@@ -22,13 +22,13 @@ def _newer(target, sources):
 
 def build_product(force=False, verbose=False):
     out = os.path.join(HERE, "libchanagpu.so")
-    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "abi.cu", "decode.cu", "headers.cu", "fanout.cu", "encode.cu", "host_table.cpp", "host_headers.cpp")]
+    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "abi.cu", "decode.cu", "headers.cu", "fanout.cu", "encode.cu", "shard.cu", "host_table.cpp", "host_headers.cpp")]
     deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "chanamq_gpu.h")]
     force = force or bool(os.environ.get("CHQ_NVCC_DEFS", "").strip())  # experiment builds never reuse a library
     if not force and not _newer(out, deps):
         return out
     cmd = [NVCC, *ARCH, "-O3", "-std=c++17", "-lineinfo", "-shared", "-Xcompiler", "-fPIC,-Wall",
-           "-cudart", "static", "-o", out, *srcs]
+           "-cudart", "static", "-o", out, *srcs, "-ldl"]
     cmd[1:1] = os.environ.get("CHQ_NVCC_DEFS", "").split()  # experiment switches, e.g. -DCHQ_PROBE_BATCH=2
     if verbose:
         cmd.insert(1, "-Xptxas=-v")

@@ -11,8 +11,12 @@ for tables that should be spread over several GPUs.  When the table fits one GPU
 compile to ~110 MB — sharding by KEYS (chanamq_b200.GpuMatcher per rank, no collective at all) moves
 far fewer bytes and is what bench.py times.
 
-The collective is injected (`Comm`): torch.distributed for real runs (nccl on GPUs, gloo in the CPU
-tests), so the host logic — slicing, declaring, gather layout, merge call — is testable without a GPU.
+Two drivers of the same layout live here:
+  ShardedExchange     the product path: libchanagpu.so's chq_shard_* (NCCL and the peer reads inside the library,
+                      one call per batch, each rank returns the finished result of its own range of messages);
+  ShardedGpuMatcher   the all-gather form spelled out with torch.distributed between two C-ABI calls (every rank ends
+                      with the whole batch's result) — kept as the readable statement of the data flow; the CPU tests
+                      run its host logic over gloo with the oracle in place of the kernels.
 """
 from typing import NamedTuple
 
@@ -136,74 +140,80 @@ class ShardedGpuMatcher:
             raise RuntimeError("sharded route: status local %d merge %d (capacity too small?)" % (s_local, s_merge))
         return out_off, out_ids[: int(tot[2])], out_dur, loc_err
 
-    def route_device_owned(self, d_blob, d_off, n, slice_cap, out_cap):
-        """The same routing with the MERGE sharded too: rank g owns the messages [g*n/G, (g+1)*n/G).  Every rank still
-        routes all n keys against its binding slice, but then only the small arrays (offsets, durable flags) are
-        all-gathered; the queue ids travel by all-to-all — each rank receives, from every slice, just the ids of the
-        messages it owns — and each rank merges its own range.  Every id crosses NVLink at most once and is merged
-        once (the all-gather form moves and merges everything on every rank).
-        -> (m0, m1, offsets int32[m1-m0+1], ids int32[total], any_durable uint8[m1-m0]) for this rank's range"""
-        torch, dist = self.torch, self.torch.distributed
-        dev = d_blob.device
-        st = torch.cuda.current_stream().cuda_stream
-        g = self.world
-        marks = []
 
-        def mk(name):   # stage marks for bench_sharded.py (self.trace = True): CUDA events on the current stream
-            if getattr(self, "trace", False):
-                e = torch.cuda.Event(enable_timing=True)
-                e.record()
-                marks.append((name, e))
+class ShardedExchange:
+    """One rank of a binding-sliced exchange through the C ABI (chq_shard_*, include/chanamq_gpu.h): one process per
+    GPU.  `unique_id` = bytes from ShardedExchange.unique_id() on one rank, handed to the others by the caller."""
 
-        mk("start")
-        loc_off = torch.empty(n + 1, dtype=torch.int32, device=dev)
-        loc_ids = torch.empty(slice_cap, dtype=torch.int32, device=dev)
-        loc_dur = torch.empty(n, dtype=torch.uint8, device=dev)
-        loc_err = torch.empty(n, dtype=torch.uint8, device=dev)
-        tot = torch.zeros(4, dtype=torch.int64, device=dev)
-        self.local.route_device(d_blob.data_ptr(), d_off.data_ptr(), n, loc_off.data_ptr(), loc_ids.data_ptr(), slice_cap,
-                                loc_dur.data_ptr(), loc_err.data_ptr(), tot.data_ptr(), tot.data_ptr() + 8, st)
-        mk('local route')
-        all_off = torch.empty(g * (n + 1), dtype=torch.int32, device=dev)
-        all_dur = torch.empty(g * n, dtype=torch.uint8, device=dev)
-        dist.all_gather_into_tensor(all_off, loc_off)
-        dist.all_gather_into_tensor(all_dur, loc_dur)
-        mk('all-gather offsets+flags')
-        all_off = all_off.view(g, n + 1)
-        bounds = [(r * n) // g for r in range(g + 1)]                      # message ranges of the owners
-        cuts = all_off[:, bounds].to(torch.int64).cpu()                    # [slice][owner boundary]: one small read-back
-        if int(tot[1].item()) & 0xFFFFFFFF:
-            raise RuntimeError("sharded route: local status %d (slice_cap too small?)" % (int(tot[1].item()) & 0xFFFFFFFF))
-        m0, m1 = bounds[self.rank], bounds[self.rank + 1]
-        send = [int(cuts[self.rank, r + 1] - cuts[self.rank, r]) for r in range(g)]      # my slice's ids for owner r
-        recv = [int(cuts[r, self.rank + 1] - cuts[r, self.rank]) for r in range(g)]      # slice r's ids for my range
-        cap = max(max(recv), 1)
-        got = torch.empty(g * cap, dtype=torch.int32, device=dev)
-        base = int(cuts[self.rank, 0])
-        ins, outs, at = [], [], base
-        for r in range(g):
-            ins.append(loc_ids[at:at + send[r]])
-            at += send[r]
-            outs.append(got[r * cap:r * cap + recv[r]])
-        dist.all_to_all(outs, ins)
-        mk('all-to-all ids')
-        nn = m1 - m0
-        sub_off = (all_off[:, m0:m1 + 1] - all_off[:, m0:m0 + 1]).contiguous()
-        sub_dur = all_dur.view(g, n)[:, m0:m1].contiguous()
-        mk('rebase')
-        out_off = torch.empty(nn + 1, dtype=torch.int32, device=dev)
-        out_ids = torch.empty(out_cap, dtype=torch.int32, device=dev)
-        out_dur = torch.empty(max(nn, 1), dtype=torch.uint8, device=dev)
-        from ._lib import check
+    @staticmethod
+    def unique_id():
+        import ctypes as C
 
-        check(self.local.L.chq_merge_slices_device2(self.device, sub_off.data_ptr(), got.data_ptr(), cap, sub_dur.data_ptr(), g, nn,
-                                                    out_off.data_ptr(), out_ids.data_ptr(), out_cap, out_dur.data_ptr(),
-                                                    tot.data_ptr() + 16, tot.data_ptr() + 24, 1 if self.disjoint else 0, st))
-        mk("merge")
-        torch.cuda.synchronize()
-        if marks:
-            self.last_stages = {b[0]: a[1].elapsed_time(b[1]) for a, b in zip(marks, marks[1:])}
-        s_merge = int(tot[3]) & 0xFFFFFFFF
-        if s_merge:
-            raise RuntimeError("sharded route: merge status %d (out_cap too small?)" % s_merge)
-        return m0, m1, out_off, out_ids[: int(tot[2])], out_dur[:nn]
+        from ._lib import CHQ_OK, ChqError, load_library
+
+        L = load_library()
+        buf = (C.c_uint8 * 128)()
+        rc = L.chq_shard_unique_id(buf)
+        if rc != CHQ_OK:
+            raise ChqError(rc, (L.chq_shard_last_error() or b"").decode())
+        return bytes(buf)
+
+    def __init__(self, unique_id, rank, world, device, exchange_type, mode):
+        import ctypes as C
+
+        from ._lib import load_library
+
+        self.L = load_library()
+        self.rank, self.world, self.device = rank, world, device
+        self.h = C.c_void_p()
+        idb = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        self._check(self.L.chq_shard_create(C.byref(self.h), idb, rank, world, device, exchange_type, mode))
+
+    def _check(self, rc):
+        from ._lib import CHQ_OK, ChqError
+
+        if rc != CHQ_OK:
+            text = (self.L.chq_shard_last_error() or b"").decode("utf-8", "replace") or (self.L.chq_last_error() or b"").decode()
+            raise ChqError(rc, text)
+
+    def close(self):
+        if self.h:
+            self.L.chq_shard_destroy(self.h)
+            self.h = None
+
+    def bind_many(self, key_blob, key_off, queue_blob, queue_off, durable, first_index=0):
+        """the WHOLE binding list on every rank: binding i is kept by rank (first_index + i) mod world"""
+        kb = np.ascontiguousarray(key_blob, dtype=np.uint8)
+        ko = np.ascontiguousarray(key_off, dtype=np.uint32)
+        qb = np.ascontiguousarray(queue_blob, dtype=np.uint8)
+        qo = np.ascontiguousarray(queue_off, dtype=np.uint32)
+        du = np.ascontiguousarray(durable, dtype=np.uint8)
+        self._check(self.L.chq_shard_bind_many(self.h, kb.ctypes.data, ko.ctypes.data, qb.ctypes.data, qo.ctypes.data,
+                                               du.ctypes.data, len(ko) - 1, first_index))
+
+    def commit(self):
+        self._check(self.L.chq_shard_commit(self.h))
+
+    @property
+    def disjoint(self):
+        return bool(self.L.chq_shard_is_disjoint(self.h))
+
+    def reserve(self, max_keys, slice_cap, pull_cap):
+        self._check(self.L.chq_shard_reserve(self.h, max_keys, slice_cap, pull_cap))
+
+    def route_device(self, d_blob, d_off, n, d_offsets, d_ids, ids_cap, d_durable, d_err, d_total, d_status, stream=0):
+        """raw device pointers; asynchronous on `stream` -> (first_message, end_message) of this rank's range"""
+        import ctypes as C
+
+        m0, m1 = C.c_uint32(), C.c_uint32()
+        self._check(self.L.chq_shard_route_device(self.h, d_blob, d_off, n, d_offsets, d_ids, ids_cap, d_durable, d_err, d_total,
+                                                  d_status, C.byref(m0), C.byref(m1), stream))
+        return m0.value, m1.value
+
+    def stage_ms(self, enable):
+        """-> ({stage: ms summed since the last call}, batches); then switch recording on/off"""
+        import ctypes as C
+
+        ms, n = (C.c_double * 4)(), C.c_uint32()
+        self._check(self.L.chq_shard_stage_ms(self.h, int(enable), ms, C.byref(n)))
+        return dict(zip(("local_route", "all_gather", "pull", "merge"), list(ms))), n.value

@@ -178,6 +178,51 @@ int32_t chq_merge_slices_device2(int32_t device, const uint32_t* d_slice_offsets
                                 uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable, uint64_t* d_total,
                                 int32_t* d_status, uint32_t flags, void* stream);
 
+/* ---- the same layout as ONE call per batch, with the exchange between the GPUs inside the library (NCCL over NVLink
+ *      plus direct loads from the peers' result buffers).  One process per GPU; one chq_shard per (exchange, rank).
+ *      No counterpart in the reference (entity/ExchangeEntity.scala:107).  Per batch every rank is given the SAME n
+ *      keys; rank g comes back with the finished result of ITS range of messages, [g n / G, (g+1) n / G): all ranks
+ *      together hold the batch's result, every queue id crossed NVLink at most once.
+ *        chq_shard_unique_id   on one rank; the 128 bytes reach the others by any means (the broker's own cluster
+ *                              channel, a file, MPI, torch.distributed)
+ *        chq_shard_create      collective (ncclCommInitRank): rank, world (<= 8), CUDA device of this process
+ *        chq_shard_bind_many   every rank is given the same bindings, numbered first_index, first_index + 1, ...;
+ *                              binding i is kept by rank i mod world, every queue name is declared on every rank
+ *                              (single bindings can also go through chq_shard_table + chq_bind / chq_declare_queues)
+ *        chq_shard_commit      chq_commit of the slice
+ *        chq_shard_reserve     collective: buffers for batches of up to max_keys keys; slice_cap = ids one slice may
+ *                              produce for a whole batch, pull_cap = ids of ONE slice that may fall into one rank's
+ *                              message range.  The ranks exchange cudaIpc handles of their slice buffers here.
+ *        chq_shard_route_device  collective, asynchronous on `stream`.  d_offsets[(end - first) + 1], d_queue_ids,
+ *                              d_any_durable[end - first], d_err[end - first] describe the messages [*first_message,
+ *                              *end_message) of the batch (offsets start at 0); *d_status = CHQ_OK, or the first failure
+ *                              of ANY rank's part (CHQ_E_OVERFLOW: slice_cap / pull_cap / ids_cap too small;
+ *                              CHQ_E_SCRATCH), the same on every rank — no rank is left waiting in a collective.
+ *      NCCL is loaded on first use (dlopen of libnccl.so.2, the copy already in the process if there is one); without
+ *      it these calls return CHQ_E_CUDA.  chq_shard_last_error() has the text of this file's failures. ---- */
+typedef struct chq_shard chq_shard;
+#define CHQ_SHARD_ID_BYTES 128
+int32_t chq_shard_unique_id(uint8_t* id128);
+int32_t chq_shard_create(chq_shard** out, const uint8_t* id128, int32_t rank, int32_t world, int32_t device,
+                         int32_t exchange_type, int32_t mode);
+int32_t chq_shard_destroy(chq_shard* s);
+chq_table* chq_shard_table(chq_shard* s);
+int32_t chq_shard_bind_many(chq_shard* s, const uint8_t* keys_blob, const uint32_t* key_offsets, const uint8_t* queues_blob,
+                            const uint32_t* queue_offsets, const uint8_t* durable, uint32_t n, uint32_t first_index);
+int32_t chq_shard_commit(chq_shard* s);
+/* 1 when no queue name was bound on two slices so far (the unions then skip de-duplication) */
+int32_t chq_shard_is_disjoint(const chq_shard* s);
+int32_t chq_shard_reserve(chq_shard* s, uint32_t max_keys, uint64_t slice_cap, uint64_t pull_cap);
+int32_t chq_shard_route_device(chq_shard* s, const uint8_t* d_keys_blob, const uint32_t* d_key_offsets, uint32_t n,
+                               uint32_t* d_offsets, uint32_t* d_queue_ids, uint64_t ids_cap, uint8_t* d_any_durable,
+                               uint8_t* d_err, uint64_t* d_total, int32_t* d_status, uint32_t* first_message,
+                               uint32_t* end_message, void* stream);
+/* Device time of the four stages of chq_shard_route_device (local route, all-gather, pull, merge), from CUDA events on
+ * the caller's stream: synchronises the device, returns the sums (ms) over the batches since the last call (at most 64
+ * are kept), then switches recording on or off. */
+int32_t chq_shard_stage_ms(chq_shard* s, int32_t enable, double* stage_ms, uint32_t* batches);
+const char* chq_shard_last_error(void);
+
 /* ---- decode seam: FrameParser.onReceive (chana-mq-base/.../engine/FrameParser.scala:78-158) +
  *      CommandAssembler.onReceive (.../engine/CommandAssembler.scala:56-130) + Basic.Publish arguments
  *      (.../method/Basic.scala:45) + BasicProperties.readFrom (.../model/BasicProperties.scala:42-96) + the
