@@ -47,6 +47,10 @@ __device__ __forceinline__ uint32_t ldg_lower_bound(const uint32_t* __restrict__
   return lo - off;
 }
 
+// (Measured and not kept: galloping away from the proportional place idx * n2 / n1 when the two lists have similar
+// lengths — the slices of a sharded exchange interleave, so the answer lies next to it — 0.194 -> 0.216 ms on the
+// headline batch, 0.34 -> 0.43 ms with '#' patterns: the lanes' loops diverge and the plain bisection's loads are
+// L1 hits after the first few.)
 // gm = the lanes of this chunk whose message belongs to the group (at most kFlatGroup); (m, meta, cnt, pos) = the
 // lane's own message.  Afterwards every short id of the group's messages is in place in ids[], fb.cm[g] marks
 // those places (and everything outside the message), fb.d / fb.pos / fb.cnt describe message g for quad_stream.

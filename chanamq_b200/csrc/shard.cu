@@ -141,7 +141,31 @@ __global__ void __launch_bounds__(256) k_pull(const uint32_t* __restrict__ all_o
   }
   const uint32_t* src = peer_ids[r] + a;
   uint32_t* dst = got + (size_t)r * pull_cap;
-  for (size_t i = tid; i < take; i += nthr) dst[i] = src[i];
+  // 16-byte loads on the (possibly remote) source, four per thread in flight: a trip over NVLink takes microseconds,
+  // the link is only kept busy by many wide requests.  The source decides the alignment; the local side takes what comes.
+  const size_t head = min((size_t)((4u - (a & 3u)) & 3u), (size_t)take);
+  if (tid < head) dst[tid] = src[tid];
+  const uint4* s4 = reinterpret_cast<const uint4*>(src + head);
+  uint32_t* d = dst + head;
+  const size_t n4 = (take - head) / 4;
+  size_t i = tid;
+  for (; i + 3 * nthr < n4; i += 4 * nthr) {
+    const uint4 v0 = __ldcs(s4 + i), v1 = __ldcs(s4 + i + nthr), v2 = __ldcs(s4 + i + 2 * nthr), v3 = __ldcs(s4 + i + 3 * nthr);
+    uint32_t* o0 = d + 4 * i;
+    uint32_t* o1 = d + 4 * (i + nthr);
+    uint32_t* o2 = d + 4 * (i + 2 * nthr);
+    uint32_t* o3 = d + 4 * (i + 3 * nthr);
+    o0[0] = v0.x; o0[1] = v0.y; o0[2] = v0.z; o0[3] = v0.w;
+    o1[0] = v1.x; o1[1] = v1.y; o1[2] = v1.z; o1[3] = v1.w;
+    o2[0] = v2.x; o2[1] = v2.y; o2[2] = v2.z; o2[3] = v2.w;
+    o3[0] = v3.x; o3[1] = v3.y; o3[2] = v3.z; o3[3] = v3.w;
+  }
+  for (; i < n4; i += nthr) {
+    const uint4 v = __ldcs(s4 + i);
+    uint32_t* o = d + 4 * i;
+    o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+  }
+  for (size_t j = head + 4 * n4 + tid; j < take; j += nthr) dst[j] = src[j];
   uint32_t* o = sub_off + (size_t)r * (nn + 1);
   for (size_t j = tid; j <= nn; j += nthr) {
     const uint64_t v = so[m0 + j] - a;
