@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--mode", default="compat", choices=["compat", "spec"],
                     help="compat = the reference's semantics ('#' is a word); spec = AMQP '#' wildcard")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa", action="store_true", help="leave the process where the launcher put it (default: move it to its GPU's NUMA node)")
     ap.add_argument("--cpu-sample", type=int, default=100_000)
     ap.add_argument("--ref-sample", type=int, default=0, help="keys per reference-arm step (0 = sized from a pilot so that the run takes about 75 s)")
     return ap.parse_args()
@@ -182,6 +183,10 @@ def run_ours(a, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=dev)
 
     L = load_library()
+    # this process on its GPU's NUMA node before anything is allocated (pinned staging and result buffers follow it)
+    numa_node, numa_cpus = C.c_int32(-1), C.c_int32(0)
+    if not a.no_numa:
+        L.chq_numa_bind_to_device(local_rank, C.byref(numa_node), C.byref(numa_cpus))
     w, binds = make_table_inputs(a)
     t0 = time.perf_counter()
     m = GpuMatcher(CHQ_TOPIC, CHQ_MODE_COMPAT if a.mode == "compat" else CHQ_MODE_SPEC, device=local_rank)
@@ -319,7 +324,8 @@ def run_ours(a, rank, world, local_rank):
                        "sharding": "keys (table replicated per GPU, no data-path collective)",
                        "l2": "10 distinct resident batches rotate; each step writes ~%.0f MB of ids (> 126 MB L2)" % (ids_per_batch * 4 / 1e6),
                        "table": {k: st[k] for k in ("bindings", "queues", "groups", "shapes", "words", "wstride", "table_bytes")},
-                       "table_build_s": build_s},
+                       "table_build_s": build_s,
+                       "numa": {"node_rank0": numa_node.value, "cpus_rank0": numa_cpus.value} if not a.no_numa else None},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / a.steps, "pipeline_depth": depth, "checksum_ids": chk,
                     "timing": "host wall clock around K pipelined chq_route_submit/chq_route_wait calls, pinned host keys in, host CSR out"},

@@ -54,6 +54,7 @@ def load_library():
         "chq_unbind": (i32, [vp, C.c_char_p, u32, C.c_char_p, u32, u8]),
         "chq_unbind_queue": (i32, [vp, C.c_char_p, u32]),
         "chq_commit": (i32, [vp]),
+        "chq_commit_full": (i32, [vp]),
         "chq_n_queues": (i32, [vp, C.POINTER(u32)]),
         "chq_queue_name": (i32, [vp, u32, C.POINTER(vp), C.POINTER(u32)]),
         "chq_route": (i32, [vp, vp, vp, u32, vp, vp, C.POINTER(ChqResult)]),
@@ -84,6 +85,7 @@ def load_library():
         "chq_fanout_last_error": (C.c_char_p, []),
         "chq_deliver_encode_device": (i32, [vp, vp, u64, vp, vp, u32, u32, vp, u64, vp, vp, vp]),
         "chq_encode_last_error": (C.c_char_p, []),
+        "chq_numa_bind_to_device": (i32, [i32, C.POINTER(i32), C.POINTER(i32)]),
         "chq_host_alloc": (i32, [C.POINTER(vp), u64]),
         "chq_host_free": (i32, [vp]),
         "chq_stats": (i32, [vp, C.c_char_p, u32]),
@@ -91,6 +93,7 @@ def load_library():
         "chq_profile_kernels": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(u32)]),
         "chq_kernel_launches": (u64, []),
         "chq_debug_limits": (i32, [vp, u32, u32]),
+        "chq_debug_check": (i32, [vp]),
         "chq_debug_clocks": (i32, [C.POINTER(C.c_uint64)]),
     }
     for name, (res, args) in sig.items():

@@ -141,6 +141,8 @@ struct chq_table {
   std::atomic<bool> committed{false};   // device copy is current: routing allowed
   std::atomic<bool> compiled{false};    // ct is current: queue names / stats valid
   bool host_only = false;   // device == -1: compile-only table for host-side checks, cannot route
+  bool uploaded = false;    // a full compile has been uploaded: later commits may patch it in place
+  uint64_t n_full = 0, n_incremental = 0;
   int device = 0, n_sms = 148;
   // device copy of the compiled table
   DevBuf<DictSlot> d_dict;
@@ -456,22 +458,92 @@ int32_t chq_declare_queues(chq_table* t, const uint8_t* queues_blob, const uint3
   return CHQ_OK;
 }
 
-int32_t chq_commit(chq_table* t) {
-  if (!t) return fail(CHQ_E_ARG, "chq_commit: bad argument");
+namespace {
+
+// The changes an incremental commit made on the host, copied over the device copy (a handful of small copies per
+// bind).  false = an array outgrew its device buffer: the caller uploads the whole table again.
+int patch_table(chq_table* t, const std::vector<Patch>& patches, bool* fits) {
+  CompiledTable& c = t->ct;
+  *fits = c.wdict.size() <= t->d_wdict.cap && c.wdict_off.size() <= t->d_wdict_off.cap && c.dict_bytes.size() <= t->d_dict_bytes.cap &&
+          c.tags.size() <= t->d_tags.cap && c.slot_group.size() <= t->d_slot_group.cap && c.groups.size() <= t->d_groups.cap &&
+          c.lits.size() <= t->d_lits.cap && c.rems.size() <= t->d_rems.cap && c.qlist.size() <= t->d_qlist.cap;
+  if (!*fits) return CHQ_OK;
+  for (const Patch& p : patches) {
+    if (p.n == 0) continue;
+    switch (p.array) {
+      case kPaWdict: CU(cudaMemcpy(t->d_wdict.p + p.off, c.wdict.data() + p.off, p.n * sizeof(WordSlot), cudaMemcpyHostToDevice)); break;
+      case kPaWdictOff: CU(cudaMemcpy(t->d_wdict_off.p + p.off, c.wdict_off.data() + p.off, p.n * 4, cudaMemcpyHostToDevice)); break;
+      case kPaDictBytes: CU(cudaMemcpy(t->d_dict_bytes.p + p.off, c.dict_bytes.data() + p.off, p.n, cudaMemcpyHostToDevice)); break;
+      case kPaTags: CU(cudaMemcpy(t->d_tags.p + p.off, c.tags.data() + p.off, p.n * 2, cudaMemcpyHostToDevice)); break;
+      case kPaSlotGroup: CU(cudaMemcpy(t->d_slot_group.p + p.off, c.slot_group.data() + p.off, p.n * 4, cudaMemcpyHostToDevice)); break;
+      case kPaGroups: CU(cudaMemcpy(t->d_groups.p + p.off, c.groups.data() + p.off, p.n * sizeof(Group), cudaMemcpyHostToDevice)); break;
+      case kPaLits: CU(cudaMemcpy(t->d_lits.p + p.off, c.lits.data() + p.off, p.n * 4, cudaMemcpyHostToDevice)); break;
+      case kPaRems: CU(cudaMemcpy(t->d_rems.p + p.off, c.rems.data() + p.off, p.n * 4, cudaMemcpyHostToDevice)); break;
+      case kPaQlist: CU(cudaMemcpy(t->d_qlist.p + p.off, c.qlist.data() + p.off, p.n * 4, cudaMemcpyHostToDevice)); break;
+      default: break;
+    }
+  }
+  // (a copy from pageable memory returns once the bytes are staged, not once they have landed: the batches that
+  // follow run on non-blocking streams and must not overtake them)
+  CU(cudaStreamSynchronize(nullptr));
+  t->tv.n_groups = (uint32_t)c.groups.size();
+  return CHQ_OK;
+}
+
+int commit_impl(chq_table* t, bool allow_incremental) {
   std::lock_guard<std::mutex> g(t->mu);
-  if (t->host_only) {
-    t->host.compile(t->ct);
+  if (t->host_only) {  // no device copy: the same decision, host side only
+    std::vector<Patch> patches;
+    if (allow_incremental && t->uploaded && t->host.incremental_ready() && t->host.apply_pending(t->ct, patches)) {
+      t->n_incremental++;
+    } else {
+      t->host.compile(t->ct);
+      t->uploaded = true;
+      t->n_full++;
+    }
     t->compiled = true;
     return CHQ_OK;
   }
   int rc = set_device(t);
   if (rc) return rc;
+  // In place when the table is on the device already and the changes allow it (host_inc.cpp): the reference's bind is
+  // O(depth) and visible at once (QueueMatcher.scala:385-392); here it is a few small copies behind the batches in
+  // flight.  Anything else: compile the whole binding set again.
+  if (allow_incremental && t->uploaded && t->host.incremental_ready()) {
+    std::vector<Patch> patches;
+    if (t->host.apply_pending(t->ct, patches)) {
+      t->compiled = true;
+      if (!patches.empty()) {
+        CU(cudaDeviceSynchronize());  // nothing in flight may read a half-patched table
+        bool fits = false;
+        if ((rc = patch_table(t, patches, &fits))) return rc;
+        if (!fits && (rc = upload_table(t))) return rc;
+      }
+      t->n_incremental++;
+      t->committed = true;
+      return CHQ_OK;
+    }
+  }
   CU(cudaDeviceSynchronize());  // nothing in flight may still read the old table
   t->host.compile(t->ct);
   t->compiled = true;
   if ((rc = upload_table(t))) return rc;
+  t->uploaded = true;
+  t->n_full++;
   t->committed = true;
   return CHQ_OK;
+}
+
+}  // namespace
+
+int32_t chq_commit(chq_table* t) {
+  if (!t) return fail(CHQ_E_ARG, "chq_commit: bad argument");
+  return commit_impl(t, true);
+}
+
+int32_t chq_commit_full(chq_table* t) {
+  if (!t) return fail(CHQ_E_ARG, "chq_commit_full: bad argument");
+  return commit_impl(t, false);
 }
 
 int32_t chq_n_queues(const chq_table* t, uint32_t* n) {
@@ -821,11 +893,13 @@ int32_t chq_stats(const chq_table* t, char* json, uint32_t cap) {
   int w = snprintf(json, cap,
                    "{\"bindings\": %llu, \"queues\": %zu, \"groups\": %zu, \"heads\": %llu, \"shapes\": %zu, "
                    "\"words\": %zu, \"pattern_words\": %llu, \"wstride\": %u, \"table_bytes\": %llu, "
-                   "\"batches\": %llu, \"messages\": %llu, \"ids\": %llu, \"committed\": %s}",
+                   "\"batches\": %llu, \"messages\": %llu, \"ids\": %llu, \"full_commits\": %llu, "
+                   "\"incremental_commits\": %llu, \"committed\": %s}",
                    (unsigned long long)c.n_bindings, c.queue_names.size(), c.groups.size(), (unsigned long long)c.n_heads,
                    c.shapes.size(), (size_t)c.n_words, (unsigned long long)c.pattern_words, c.wstride,
                    (unsigned long long)table_bytes, (unsigned long long)t->n_batches, (unsigned long long)t->n_messages,
-                   (unsigned long long)t->n_ids, t->compiled ? "true" : "false");
+                   (unsigned long long)t->n_ids, (unsigned long long)t->n_full, (unsigned long long)t->n_incremental,
+                   t->compiled ? "true" : "false");
   return (w < 0 || (uint32_t)w >= cap) ? fail(CHQ_E_ARG, "chq_stats: buffer too small") : CHQ_OK;
 }
 
@@ -877,6 +951,33 @@ int32_t chq_debug_clocks(uint64_t* out32) {
   CU(cudaDeviceSynchronize());
   static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "");
   CU(read_clocks(reinterpret_cast<unsigned long long*>(out32)));
+  return CHQ_OK;
+}
+
+int32_t chq_debug_check(chq_table* t) {
+  // test hook: structural invariants of the compiled table on the host (after in-place commits above all)
+  if (!t) return fail(CHQ_E_ARG, "chq_debug_check: bad argument");
+  std::lock_guard<std::mutex> g(t->mu);
+  const CompiledTable& c = t->ct;
+  if (c.headers_mode) return CHQ_OK;
+  std::vector<uint32_t> uses(c.queue_names.size(), 0);
+  for (size_t gi = 0; gi < c.groups.size(); ++gi) {
+    const Group& gr = c.groups[gi];
+    if ((size_t)gr.list_off + gr.list_len > c.qlist.size()) return fail(CHQ_E_ARG, "group " + std::to_string(gi) + ": list outside qlist");
+    for (uint32_t i = 0; i < gr.list_len; ++i) {
+      const uint32_t q = c.qlist[gr.list_off + i];
+      if (q >= c.queue_names.size()) return fail(CHQ_E_ARG, "group " + std::to_string(gi) + ": id out of range");
+      if (i && c.qlist[gr.list_off + i - 1] >= q) return fail(CHQ_E_ARG, "group " + std::to_string(gi) + ": list not ascending");
+      uses[q]++;
+    }
+    if (gr.shape >= c.shapes.size()) return fail(CHQ_E_ARG, "group " + std::to_string(gi) + ": shape out of range");
+  }
+  for (size_t gi = 0; gi < c.groups.size(); ++gi) {
+    const Group& gr = c.groups[gi];
+    for (uint32_t i = 0; i < gr.list_len; ++i)
+      if (uses[c.qlist[gr.list_off + i]] > 1 && !(gr.flags & kShared))
+        return fail(CHQ_E_ARG, "group " + std::to_string(gi) + ": shares a queue with another group but is not flagged");
+  }
   return CHQ_OK;
 }
 

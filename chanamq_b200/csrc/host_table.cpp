@@ -47,7 +47,8 @@ int HostTable::bind(std::string_view key, std::string_view queue, bool durable, 
   int rc = check_key(key);
   if (rc != CHQ_OK) return rc;
   if (!args.empty() && !valid_field_table(args)) return CHQ_E_ARG;
-  live_.emplace(std::string(key), std::string(queue), durable, std::string(args));
+  const bool fresh = live_.emplace(std::string(key), std::string(queue), durable, std::string(args)).second;
+  if (fresh && inc_.valid) pending_.push_back(Op{true, std::string(key), std::string(queue), durable});
   return CHQ_OK;
 }
 
@@ -56,15 +57,23 @@ int HostTable::unbind(std::string_view key, std::string_view queue, bool durable
   if (rc != CHQ_OK) return rc;
   // queueUnbind(queue, routingKey) ignores the arguments (ExchangeEntity.scala:370-382): every variant goes
   auto it = live_.lower_bound(std::make_tuple(std::string(key), std::string(queue), durable, std::string()));
-  while (it != live_.end() && std::get<0>(*it) == key && std::get<1>(*it) == queue && std::get<2>(*it) == durable)
+  bool any = false;
+  while (it != live_.end() && std::get<0>(*it) == key && std::get<1>(*it) == queue && std::get<2>(*it) == durable) {
     it = live_.erase(it);
+    any = true;
+  }
+  if (any && inc_.valid) pending_.push_back(Op{false, std::string(key), std::string(queue), durable});
   return CHQ_OK;
 }
 
 int HostTable::unbind_queue(std::string_view queue) {
   for (auto it = live_.begin(); it != live_.end();) {
-    if (std::get<1>(*it) == queue) it = live_.erase(it);
-    else ++it;
+    if (std::get<1>(*it) == queue) {
+      if (inc_.valid) pending_.push_back(Op{false, std::get<0>(*it), std::get<1>(*it), std::get<2>(*it)});
+      it = live_.erase(it);
+    } else {
+      ++it;
+    }
   }
   return CHQ_OK;
 }
@@ -89,14 +98,6 @@ uint32_t pow2_at_least(uint64_t x) {
   while (p < x) p <<= 1;
   return p;
 }
-
-struct VecHash {  // FNV-style hash of an encoded pattern
-  size_t operator()(const std::vector<uint32_t>& v) const {
-    uint64_t h = 0xCBF29CE484222325ull;
-    for (uint32_t x : v) h = (h ^ x) * 0x100000001B3ull;
-    return (size_t)(h ^ (h >> 29));
-  }
-};
 
 struct GroupBuild {
   uint32_t shape_key;  // index into the unsorted shape list
@@ -129,6 +130,8 @@ void HostTable::compile(CompiledTable& out) const {
     t_prev = now;
   };
   out = CompiledTable();
+  inc_ = Inc();        // rebuilt at the end (topic / direct tables); the changes queued for it are in this compile
+  pending_.clear();
   out.n_bindings = live_.size();
   out.exact_rng.assign(3 * (kLenCap + 1), 0);
 
@@ -298,11 +301,13 @@ void HostTable::compile(CompiledTable& out) const {
   out.wstride = any_complex ? (uint32_t)kMaxWords : std::max<uint32_t>(4, (max_len + 3) & ~3u);
 
   // groups, literal tuples, remainders, queue lists; "shared" = some queue sits in two groups
-  std::vector<uint32_t> queue_uses(out.queue_names.size(), 0);
-  for (auto& g : gb) {
+  std::vector<uint32_t> queue_uses(out.queue_names.size(), 0), first_group(out.queue_names.size(), kNone);
+  for (uint32_t gi = 0; gi < gb.size(); ++gi) {
+    GroupBuild& g = gb[gi];
     std::sort(g.queues.begin(), g.queues.end());
     g.queues.erase(std::unique(g.queues.begin(), g.queues.end()), g.queues.end());
-    for (uint32_t q : g.queues) queue_uses[q]++;
+    for (uint32_t q : g.queues)
+      if (queue_uses[q]++ == 0) first_group[q] = gi;
   }
   out.groups.resize(gb.size());
   // chain heads keyed by (shape, literal tuple): groups that differ only in their remainder share one
@@ -398,6 +403,23 @@ void HostTable::compile(CompiledTable& out) const {
     }
   }
   if (out.dict_bytes.empty()) out.dict_bytes.push_back(0);
+
+  // what single binds need later to be added in place (host_inc.cpp)
+  inc_.words.reserve(words.size() * 2);
+  for (auto& kv : words) inc_.words.emplace(std::string(kv.first), kv.second);
+  inc_.shape_ids = std::move(shape_ids);
+  inc_.new_shape = std::move(new_shape);
+  inc_.group_ids = std::move(group_ids);
+  inc_.heads = std::move(heads);
+  inc_.qid.reserve(out.queue_names.size() * 2);
+  for (uint32_t i = 0; i < out.queue_names.size(); ++i) inc_.qid.emplace(out.queue_names[i], i);
+  inc_.queue_uses = std::move(queue_uses);
+  inc_.first_group = std::move(first_group);
+  inc_.list_cap.resize(out.groups.size());
+  for (uint32_t gi = 0; gi < out.groups.size(); ++gi) inc_.list_cap[gi] = out.groups[gi].list_len;
+  inc_.max_len = max_len;
+  inc_.valid = true;
+  lap("state for incremental commits");
 }
 
 }  // namespace chq

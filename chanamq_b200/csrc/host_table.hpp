@@ -6,7 +6,9 @@
 // publish, ExchangeEntity.scala:187-285).
 #pragma once
 #include <cstdint>
+#include <map>
 #include <set>
+#include <unordered_map>
 #include <string>
 #include <string_view>
 #include <tuple>
@@ -49,6 +51,19 @@ void java_split(std::string_view s, std::vector<std::string_view>& out);
 // hash of a word / field name / value: word_chunk over 8-byte chunks from `seed`, then word_fin with the length
 uint32_t bytes_hash(uint32_t seed, std::string_view w);
 
+// One piece of a committed table that an incremental commit changed on the host: elements [off, off + n) of one of
+// its arrays, to be copied over the device copy.
+enum PatchArray { kPaWdict, kPaWdictOff, kPaDictBytes, kPaTags, kPaSlotGroup, kPaGroups, kPaLits, kPaRems, kPaQlist, kPaCount };
+struct Patch { int array; size_t off, n; };
+
+struct VecHash {  // FNV-style hash of an encoded pattern
+  size_t operator()(const std::vector<uint32_t>& v) const {
+    uint64_t h = 0xCBF29CE484222325ull;
+    for (uint32_t x : v) h = (h ^ x) * 0x100000001B3ull;
+    return (size_t)(h ^ (h >> 29));
+  }
+};
+
 class HostTable {
  public:
   HostTable(int exchange_type, int mode) : type_(exchange_type), mode_(mode) {}
@@ -59,7 +74,13 @@ class HostTable {
   int unbind_queue(std::string_view queue);
   // a queue that takes part in the id numbering although nothing is bound to it HERE (binding-slice
   // sharding: every GPU numbers the queues of the whole exchange, so ids agree across slices)
-  void declare_queue(std::string_view queue) { declared_.emplace(queue); }
+  void declare_queue(std::string_view queue) { declared_.emplace(queue); inc_.valid = false; }
+  // Incremental commit (host_inc.cpp): applies the binds / unbinds made since the last commit to an already compiled
+  // table in place and lists what changed.  false = this set of changes needs a full compile() (a pattern shape the
+  // table has not seen, a hash index or dictionary that got too full, a '#' that widens the word rows, ...).
+  bool apply_pending(CompiledTable& ct, std::vector<Patch>& patches) const;
+  size_t pending() const { return pending_.size(); }
+  bool incremental_ready() const { return inc_.valid; }
   void compile(CompiledTable& out) const;
   size_t size() const { return live_.size(); }
   int type() const { return type_; }
@@ -72,6 +93,24 @@ class HostTable {
   void compile_headers(CompiledTable& out) const;  // host_headers.cpp
   std::set<std::tuple<std::string, std::string, bool, std::string>> live_;
   std::set<std::string> declared_;
+  // what compile() knew when it built the table, kept so that single binds can be added to it (host_inc.cpp)
+  struct Inc {
+    bool valid = false;
+    std::unordered_map<std::string, uint32_t> words;                        // pattern word -> id
+    std::map<std::tuple<uint8_t, uint8_t, uint32_t>, uint32_t> shape_ids;   // (kind, len, mask) -> number in meeting order
+    std::vector<uint32_t> new_shape;                                        // that number -> position in CompiledTable::shapes
+    std::unordered_map<std::vector<uint32_t>, uint32_t, VecHash> group_ids; // encoded pattern -> group
+    std::unordered_map<std::vector<uint32_t>, uint32_t, VecHash> heads;     // (shape, literal tuple) -> chain head
+    std::unordered_map<std::string, uint32_t> qid;                          // queue name -> id
+    std::vector<uint32_t> queue_uses, first_group;                          // per queue: groups that list it, one of them
+    std::vector<uint32_t> list_cap;                                         // per group: room of its list in qlist
+    uint32_t max_len = 1;
+  };
+  mutable Inc inc_;
+  struct Op { bool bind; std::string key, queue; bool durable; };
+  mutable std::vector<Op> pending_;
+  bool apply_bind(CompiledTable& ct, std::vector<Patch>& patches, const Op& op) const;
+  bool apply_unbind(CompiledTable& ct, std::vector<Patch>& patches, const Op& op) const;
 };
 
 }  // namespace chq

@@ -272,7 +272,7 @@ int32_t chq_shard_bind_many(chq_shard* s, const uint8_t* keys_blob, const uint32
 
 int32_t chq_shard_commit(chq_shard* s) {
   if (!s) return sfail(CHQ_E_ARG, "chq_shard_commit: bad argument");
-  int rc = chq_commit(s->table);
+  int rc = chq_commit_full(s->table);   // every slice must number the queues alike: by name rank
   if (rc) g_shard_err = chq_last_error();
   return rc;
 }

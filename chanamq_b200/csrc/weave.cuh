@@ -102,10 +102,12 @@ __device__ __forceinline__ void warp_weave(const uint32_t* __restrict__ qlist, u
   //      at most 32, else ws.b[0 .. ns) ----
   uint32_t s = kNone, ns;
   bool hole = false;
+  bool in_regs = true;   // the short ids sit one per lane (at most 32 of them before duplicates go), else in ws.b
   if (k == 2) {  // one short list: it is sorted already
     ns = __shfl_sync(kFull, my_len, 1);
     const uint32_t o = __shfl_sync(kFull, my_off, 1);
-    if (ns <= 32) {
+    in_regs = ns <= 32;
+    if (in_regs) {
       if ((uint32_t)lane < ns) s = __ldg(qlist + o + lane);
     } else {
       for (uint32_t i = lane; i < ns; i += 32) ws.b[i] = __ldg(qlist + o + i);
@@ -120,7 +122,8 @@ __device__ __forceinline__ void warp_weave(const uint32_t* __restrict__ qlist, u
     }
     ns = __shfl_sync(kFull, incl, kRouteSlots - 1);
     const uint32_t st = incl - short_len;
-    if (ns <= 32) {
+    in_regs = ns <= 32;   // (decided before duplicates are removed: the ids stay where they were put)
+    if (in_regs) {
       if (k == 3) {  // two sorted lists: one up from lane 0, one down from lane 31 -> a bitonic sequence
         const uint32_t o1 = __shfl_sync(kFull, my_off, 1), l1 = __shfl_sync(kFull, my_len, 1);
         const uint32_t o2 = __shfl_sync(kFull, my_off, 2), l2 = __shfl_sync(kFull, my_len, 2);
@@ -175,7 +178,6 @@ __device__ __forceinline__ void warp_weave(const uint32_t* __restrict__ qlist, u
       if (dedup) ns = warp_unique(ws.b, ns, lane);
     }
   }
-  const bool in_regs = ns <= 32;   // (ns before the removal of duplicates decides: the ids are where they were put)
   __syncwarp();
 
   // ---- tiles of the long list ----

@@ -137,7 +137,14 @@ class GpuMatcher:
         self._dirty = True
 
     def commit(self):
+        """in place where the changes allow it, else a full compile (chq_commit)"""
         check(self.L.chq_commit(self.h))
+        self._dirty = False
+        self._names = None
+
+    def commit_full(self):
+        """compile the whole binding set again: queue ids become name ranks again (chq_commit_full)"""
+        check(self.L.chq_commit_full(self.h))
         self._dirty = False
         self._names = None
 

@@ -80,9 +80,19 @@ int32_t chq_unbind(chq_table* t, const uint8_t* key, uint32_t key_len, const uin
                    uint8_t durable);
 /* queueUnbind(queue): drop every binding of a deleted queue (entity/ExchangeEntity.scala:344-351) */
 int32_t chq_unbind_queue(chq_table* t, const uint8_t* queue, uint32_t queue_len);
-/* Compile the binding set and upload it.  Queue ids are assigned here: the rank of the queue name
- * among names that hold a binding, ascending by bytes, so ascending id = canonical order. */
+/* Make the binds / unbinds since the last commit visible to routing.
+ * The first commit (and chq_commit_full always) compiles the whole binding set and uploads it; queue ids are assigned
+ * there: the rank of the queue name among names that hold a binding, ascending by bytes, so ascending id = canonical
+ * order.  Later commits apply the changes IN PLACE where they can (the reference's subscribe is O(depth) and visible
+ * at once, engine/QueueMatcher.scala:385-392, 415-460): a new queue on a known or new pattern, a new pattern word, an
+ * unbind — microseconds of host work and a few small copies behind the batches in flight.  A queue name the table has
+ * not seen takes the next free id, so until the next full commit ascending id is still the order inside a result but
+ * no longer name order for those queues; a queue that lost its last binding keeps its id (and stays in
+ * chq_queue_name) until then.  Changes that cannot be made in place (a pattern shape the table has not
+ * seen, an index more than half full, a '#' that widens the word rows, fan-out and headers tables, more than 4096
+ * changes at once) fall back to the full compile by themselves.  chq_stats counts both kinds. */
 int32_t chq_commit(chq_table* t);
+int32_t chq_commit_full(chq_table* t);
 int32_t chq_n_queues(const chq_table* t, uint32_t* n);
 int32_t chq_queue_name(const chq_table* t, uint32_t queue_id, const uint8_t** name, uint32_t* len);
 
@@ -327,6 +337,14 @@ int32_t chq_deliver_encode_device(const uint8_t* d_bytes, const chq_publish_rec*
                                   uint64_t out_cap, uint64_t* d_out_offsets, int32_t* d_status, void* stream);
 const char* chq_encode_last_error(void);
 
+/* No counterpart in the reference.  Puts the CALLING thread on the NUMA node of `device`: CPU affinity = that node's
+ * CPUs (within what the thread may use), memory policy = prefer that node — for everything the thread allocates from
+ * then on, the library's pinned staging and result buffers included.  Call it once per routing thread / process before
+ * chq_table_create when a box holds several GPUs: result buffers that all sit on one socket make the other socket's
+ * GPUs copy across the socket link.  *node = the node (-1: unknown or a single-node machine, nothing changed),
+ * *n_cpus = CPUs in the new affinity mask.  Linux only. */
+int32_t chq_numa_bind_to_device(int32_t device, int32_t* node, int32_t* n_cpus);
+
 /* pinned host memory for callers that want zero-copy staging (JNA: new Pointer(addr)) */
 int32_t chq_host_alloc(void** p, uint64_t bytes);
 int32_t chq_host_free(void* p);
@@ -347,6 +365,9 @@ uint64_t chq_kernel_launches(void);
 /* measurement hook: cycle totals of the write kernel by kind of message (32 counters: cycles, messages, ids per
  * bin, see kernels.cu); all zero unless the library was built with -DCHQ_CLOCKS.  Reading resets them. */
 int32_t chq_debug_clocks(uint64_t* out32);
+/* test hook: structural invariants of the compiled table on the host (lists ascending and inside the table, ids in
+ * range, every group that shares a queue with another one flagged for de-duplication); CHQ_E_ARG + text on a breach */
+int32_t chq_debug_check(chq_table* t);
 /* test hook: lower the per-message limits that select the slower merge paths (0 = default) */
 int32_t chq_debug_limits(chq_table* t, uint32_t max_slots, uint32_t max_small);
 

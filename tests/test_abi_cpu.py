@@ -41,6 +41,9 @@ def test_host_compile_of_the_reference_kat_table():
     assert m.try_bind(".", "x") == _lib.CHQ_E_ZERO_WORDS and m.try_bind("..", "x") == _lib.CHQ_E_ZERO_WORDS
     assert m.try_bind("k" * 256, "x") == _lib.CHQ_E_KEY_TOO_LONG
     m.unbind_queue("s0")
+    # applied in place: the bindings are gone, the queue keeps its id (and its place among the names) ...
+    assert m.stats()["bindings"] == 5 and m.stats()["incremental_commits"] == 1 and b"s0" in m.queue_names()
+    m.commit_full()   # ... until the whole set is compiled again
     assert m.stats()["bindings"] == 5 and b"s0" not in m.queue_names()
 
 
