@@ -23,6 +23,7 @@
 #include "probe.cuh"
 #include "weave.cuh"
 #include "flat.cuh"
+#include "kway.cuh"
 
 #ifndef CHQ_MIN_CTAS
 #define CHQ_MIN_CTAS 8
@@ -430,6 +431,12 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   else if (k <= 1) cnt = ub;
   else if (k > p.max_slots) cls = 2;
   // one long list + at most max_small other ids: k_write's staged weave (weave.cuh); more: warp_union_long
+  // lists of similar length that share nothing (the slices of a sharded exchange, several '#' patterns): staged and
+  // merged pairwise in shared memory (kway.cuh)
+  // (from four lists on, none of which dominates: otherwise streaming the longest and placing the others was
+  // measured faster)
+  else if (!dedup && k >= 4 && k <= p.max_slots && ub <= (uint32_t)kKwayMax && ub - mxlen >= 2u * mxlen && ub > 64u &&
+           p.max_small == (uint32_t)kRouteSmall) { cls = 5; cnt = ub; }
   // (nothing shared between the lists: the flat path of k_write takes a much longer short side)
   else if (ub - mxlen > ((dedup || mxlen > (uint32_t)kFlatMaxLong || p.max_small != (uint32_t)kRouteSmall) ? p.max_small
                                                                                                              : (uint32_t)kFlatMaxShort) ||
@@ -591,6 +598,8 @@ struct WriteCtx {  // the few fields of RouteParams it needs, by value (kernel p
   uint32_t* ids;
   uint64_t ids_cap;
   bool tma_ok;   // qlist is the table's own array (16-byte aligned, lists of 8+ ids start on 16-byte boundaries)
+  KwayBuf* kway; // this warp's buffers for warp_kway (they share their shared memory with ws / wb: one path at a time)
+  uint64_t* mbar; // this warp's mbarrier for the bulk copies of warp_weave
 };
 // (lo, ll) = this lane's entry of the message's list row (lane j < k: list j), fetched by the caller ahead of time.
 __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws, WeaveBuf& wb, uint32_t& phase, uint32_t lo,
@@ -604,6 +613,9 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
   } else if (cl == 4) {
     warp_gather_small<true>(p.qlist, p.desc_lists + __shfl_sync(kFull, lo, 0), kk, (mt & kMetaDedup) != 0, ws, p.ids, o, lane);
     CHQ_CLK_ADD(3, 1, c);
+  } else if (cl == 5) {
+    if (lane >= kk) lo = ll = 0;
+    warp_kway(p.qlist, lo, ll, kk, *p.kway, p.ids + o, lane);
   } else if (kk == 1) {
     const uint32_t* sp = p.qlist + __shfl_sync(kFull, lo, 0) + lane;
     uint32_t* dst = p.ids + o + lane;
@@ -617,7 +629,7 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
   } else {
     if (lane >= kk) lo = ll = 0;
     if (cl == 3) warp_union_long<true>(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, ws, p.ids, o, lane);
-    else warp_weave(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, p.tma_ok, ws, wb, phase, p.ids + o, lane);
+    else warp_weave(p.qlist, lo, ll, kk, (mt & kMetaDedup) != 0, p.tma_ok, ws, wb, p.mbar, phase, p.ids + o, lane);
 #ifdef CHQ_CLOCKS
     uint32_t sum = ll, mx = ll;
     for (int d = 16; d; d >>= 1) { sum += __shfl_xor_sync(kFull, sum, d); mx = max(mx, __shfl_xor_sync(kFull, mx, d)); }
@@ -707,8 +719,11 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RoutePa
 // The messages k_write left out, from its work list: those with long results first (so that the longest jobs start
 // first instead of being met by chance near the end), eight messages per grab, one per warp trip.
 __global__ void __launch_bounds__(kRouteThreads, 8) k_write_rest(RouteParams p) {
-  __shared__ WarpScratch ws_all[kRouteThreads / 32];
-  __shared__ WeaveBuf wb_all[kRouteThreads / 32];
+  // per warp: the scratch of the merge paths and the weave tile, or (never at the same time) the two buffers of warp_kway
+  struct WarpMem { WarpScratch ws; WeaveBuf wb; };
+  union __align__(16) WarpShared { WarpMem m; KwayBuf kb; };
+  __shared__ WarpShared sh_all[kRouteThreads / 32];
+  __shared__ uint64_t bar_all[kRouteThreads / 32];   // the bulk copies' mbarriers: outside the shared buffers
   const TableView& tv = p.tv;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t n_big = p.ctrl[kCtrlRestBig], n_all = n_big + p.ctrl[kCtrlRest];
@@ -716,13 +731,16 @@ __global__ void __launch_bounds__(kRouteThreads, 8) k_write_rest(RouteParams p) 
 #ifdef CHQ_DEBUG_SWITCHES
   if (p.debug & 1u) return;
 #endif
-  WarpScratch& ws = ws_all[warp];
-  WeaveBuf& wb = wb_all[warp];
+  WarpScratch& ws = sh_all[warp].m.ws;
+  WeaveBuf& wb = sh_all[warp].m.wb;
   uint32_t phase = 0;
-  weave_bar_init(wb, lane);
+  weave_bar_init(&bar_all[warp], lane);
   const WriteCtx wc{p.desc_lists, tv.qlist, p.mlist, p.scratch, p.ids, p.ids_cap,
-                    !p.slice_offsets && (reinterpret_cast<uintptr_t>(tv.qlist) & 15u) == 0};
-  constexpr uint32_t kPerGrab = 8;
+                    !p.slice_offsets && (reinterpret_cast<uintptr_t>(tv.qlist) & 15u) == 0, &sh_all[warp].kb, &bar_all[warp]};
+  // messages per grab: as many as keeps every warp of the grid busy (a short list handed out eight at a time would
+  // leave most warps idle while a few work through their eight one after the other), at most eight
+  const uint32_t n_warps = gridDim.x * (kRouteThreads / 32);
+  const uint32_t kPerGrab = max(1u, min(8u, n_all / n_warps));
   for (;;) {
     CHQ_CLK_T0();
     uint32_t i0 = 0;

@@ -1,0 +1,69 @@
+// k_write_rest's path for messages whose lists are of SIMILAR length and share nothing (included by kernels.cu only):
+// the slices of a binding-sliced exchange (binding i on GPU i mod G: a message's ids are spread evenly over the G
+// slice results), several '#' patterns of one publisher.  Streaming the longest list and placing every other id by
+// k - 1 searches (flat.cuh) is the wrong tool there: most ids are on the short side.  Here the lists are staged back to
+// back in shared memory and merged pairwise, level by level (2 lists: one level, 8 lists: three): every id finds its
+// place in the merged pair by ONE binary search over the partner run, in shared memory, all lanes at once.
+#pragma once
+#include "merge.cuh"
+
+namespace chq {
+namespace {
+
+constexpr int kKwayMax = 1024;   // ids of one message on this path (two buffers of that size per warp)
+
+struct __align__(16) KwayBuf {
+  uint32_t a[kKwayMax], b[kKwayMax];
+  uint32_t start[kRouteSlots + 1];   // run r = [start[r], start[r + 1])
+};
+
+// Lane j < k holds list j = qlist[my_off .. my_off + my_len), k <= kRouteSlots, total <= kKwayMax ids, no id in two
+// lists.  Writes the sorted union to out[0 .. total).
+__device__ __forceinline__ void warp_kway(const uint32_t* __restrict__ qlist, uint32_t my_off, uint32_t my_len, int k, KwayBuf& kb,
+                                          uint32_t* __restrict__ out, int lane) {
+  const uint32_t len = lane < k ? my_len : 0u;
+  uint32_t incl = len;
+#pragma unroll
+  for (int d = 1; d < kRouteSlots; d <<= 1) {
+    const uint32_t v = __shfl_up_sync(kFull, incl, d);
+    if (lane >= d) incl += v;
+  }
+  const uint32_t total = __shfl_sync(kFull, incl, kRouteSlots - 1);
+  __syncwarp();   // the previous message is done with the buffers
+  if (lane <= kRouteSlots) kb.start[lane] = lane < kRouteSlots ? incl - len : total;   // (runs past k are empty)
+  for (int j = 0; j < k; ++j) {
+    const uint32_t o = __shfl_sync(kFull, my_off, j), l = __shfl_sync(kFull, len, j), s = __shfl_sync(kFull, incl - len, j);
+    for (uint32_t i = lane; i < l; i += 32) kb.a[s + i] = __ldg(qlist + o + i);
+  }
+  __syncwarp();
+  uint32_t* A = kb.a;
+  uint32_t* B = kb.b;
+  for (int runs = k; runs > 1; runs = (runs + 1) >> 1) {
+    for (uint32_t e = lane; e < total; e += 32) {
+      int r = 0;   // the run of element e (at most eight boundaries)
+#pragma unroll
+      for (int j = 1; j < kRouteSlots; ++j) r += (j < runs && kb.start[j] <= e) ? 1 : 0;
+      const uint32_t x = A[e];
+      const int p = r ^ 1;
+      uint32_t pos = e;   // a run without a partner keeps its place
+      if (p < runs) {
+        const uint32_t ps = kb.start[p], pl = kb.start[p + 1] - ps;
+        pos = (e - kb.start[r]) + smem_lower_bound(A + ps, pl, x) + kb.start[r & ~1];   // (no ties: the lists share nothing)
+      }
+      B[pos] = x;
+    }
+    __syncwarp();
+    // runs 2 j and 2 j + 1 became run j
+    uint32_t ns = 0;
+    const int new_runs = (runs + 1) >> 1;
+    if (lane <= kRouteSlots) ns = lane < new_runs ? kb.start[2 * lane] : total;
+    __syncwarp();
+    if (lane <= kRouteSlots) kb.start[lane] = ns;
+    __syncwarp();
+    uint32_t* t = A; A = B; B = t;
+  }
+  for (uint32_t e = lane; e < total; e += 32) CHQ_ST_OUT(out + e, A[e]);
+}
+
+}  // namespace
+}  // namespace chq

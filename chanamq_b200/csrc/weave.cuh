@@ -30,30 +30,29 @@ constexpr int kWeaveChunks = (kWeaveTile + kRouteSmall + 31 + 31) / 32 + 1;  // 
 struct __align__(16) WeaveBuf {
   uint32_t tile[kWeaveTile + 4];   // +4: the bulk copy moves whole 16-byte units
   uint32_t cmask[kWeaveChunks < 32 ? 32 : kWeaveChunks];   // per output chunk: the positions that take a short id
-  uint64_t bar;                    // mbarrier of the bulk copy
-};
+};  // (the bulk copy's mbarrier is kept apart and handed in: this memory has other users between messages)
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__device__ __forceinline__ void weave_bar_init(WeaveBuf& wb, int lane) {
+__device__ __forceinline__ void weave_bar_init(uint64_t* bar, int lane) {
   if (lane == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&wb.bar)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(bar)));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncwarp();
 }
 
 // lane 0: bulk copy of `bytes` (multiple of 16) from src (16-byte aligned) into the tile
-__device__ __forceinline__ void weave_bulk_load(WeaveBuf& wb, const uint32_t* src, uint32_t bytes) {
-  const uint32_t bar = smem_addr(&wb.bar), dst = smem_addr(wb.tile);
+__device__ __forceinline__ void weave_bulk_load(WeaveBuf& wb, uint64_t* mbar, const uint32_t* src, uint32_t bytes) {
+  const uint32_t bar = smem_addr(mbar), dst = smem_addr(wb.tile);
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
 
-__device__ __forceinline__ void weave_bar_wait(WeaveBuf& wb, uint32_t parity) {
-  const uint32_t bar = smem_addr(&wb.bar);
+__device__ __forceinline__ void weave_bar_wait(uint64_t* mbar, uint32_t parity) {
+  const uint32_t bar = smem_addr(mbar);
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
@@ -83,7 +82,7 @@ __device__ __forceinline__ uint32_t tile_lower_bound(const uint32_t* tile, uint3
 // lists.  Writes the union to out[0 ...) (k_probe counted it: nothing is returned).  `phase` = parity of the
 // warp's mbarrier, flipped by every bulk copy; tma_ok = qlist is the table's own, 16-byte aligned array.
 __device__ __forceinline__ void warp_weave(const uint32_t* __restrict__ qlist, uint32_t my_off, uint32_t my_len, int k, bool dedup,
-                                           bool tma_ok, WarpScratch& ws, WeaveBuf& wb, uint32_t& phase,
+                                           bool tma_ok, WarpScratch& ws, WeaveBuf& wb, uint64_t* mbar, uint32_t& phase,
                                            uint32_t* __restrict__ out, int lane) {
   const uint32_t lanebit = 1u << lane, ltmask = lanebit - 1u;
   const uint32_t out_mis = (uint32_t)(reinterpret_cast<uintptr_t>(out) >> 2) & 31u;   // where out[0] sits in its 128-byte line
@@ -94,7 +93,7 @@ __device__ __forceinline__ void warp_weave(const uint32_t* __restrict__ qlist, u
   if (bulk) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier plain stores into the tile come first
   __syncwarp();  // every lane is done with the tile of the previous message
   if (bulk) {
-    if (lane == 0) weave_bulk_load(wb, qlist + big_off, ((tl + 3u) & ~3u) * 4u);
+    if (lane == 0) weave_bulk_load(wb, mbar, qlist + big_off, ((tl + 3u) & ~3u) * 4u);
   } else {
     for (uint32_t i = lane; i < tl; i += 32) wb.tile[i] = __ldg(qlist + big_off + i);
   }
@@ -193,7 +192,7 @@ __device__ __forceinline__ void warp_weave(const uint32_t* __restrict__ qlist, u
     wb.cmask[lane] = lane == 0 ? (1u << a0) - 1u : 0u;
     if (kWeaveChunks > 32 && lane < kWeaveChunks - 32) wb.cmask[32 + lane] = 0;
     if (bulk) {
-      weave_bar_wait(wb, phase);
+      weave_bar_wait(mbar, phase);
       phase ^= 1u;
     }
     __syncwarp();
@@ -235,7 +234,7 @@ __device__ __forceinline__ void warp_weave(const uint32_t* __restrict__ qlist, u
     tl = min(nb - tb, (uint32_t)kWeaveTile);
     __syncwarp();  // everyone has read the tile
     if (bulk) {
-      if (lane == 0) weave_bulk_load(wb, qlist + big_off + tb, ((tl + 3u) & ~3u) * 4u);
+      if (lane == 0) weave_bulk_load(wb, mbar, qlist + big_off + tb, ((tl + 3u) & ~3u) * 4u);
     } else {
       for (uint32_t i = lane; i < tl; i += 32) wb.tile[i] = __ldg(qlist + big_off + tb + i);
     }
