@@ -29,10 +29,19 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "routed msgs/sec (topic, 1M bindings)"
 UNIT = "msgs/s"
-SEED = 4            # T(seed=4, P=1 000 000, N=10 000 000)
 N_BATCHES = 10
+
+
+def seed_of(bindings):
+    """config 1 = T(seed 1, P = 1 000), config 2 = T(seed 2, P = 100 000), configs 4 (and the headline) =
+    T(seed 4, P = 1 000 000)"""
+    return {1_000: 1, 100_000: 2}.get(bindings, 4)
+
+
+def metric_name(a):
+    p = a.bindings
+    return "routed msgs/sec (topic, %s bindings)" % ("1M" if p == 1_000_000 else ("%dk" % (p // 1000) if p % 1000 == 0 else str(p)))
 
 
 def parse():
@@ -46,6 +55,8 @@ def parse():
     ap.add_argument("--mode", default="compat", choices=["compat", "spec"],
                     help="compat = the reference's semantics ('#' is a word); spec = AMQP '#' wildcard")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true",
+                    help="skip the short legs for BASELINE.json configs 2, 3 and 5 that the default 1-GPU run appends")
     ap.add_argument("--no-numa", action="store_true", help="leave the process where the launcher put it (default: move it to its GPU's NUMA node)")
     ap.add_argument("--cpu-sample", type=int, default=100_000)
     ap.add_argument("--ref-sample", type=int, default=0, help="keys per reference-arm step (0 = sized from a pilot so that the run takes about 75 s)")
@@ -55,7 +66,7 @@ def parse():
 def workload_name(a):
     return ("topic exchange, %d bindings with mixed */# patterns (T(seed=%d), one queue per binding), %s semantics, "
             "batches of %d keys x %d resident batches" % (
-                a.bindings, SEED, "reference (COMPAT: '#' literal)" if a.mode == "compat" else "AMQP (SPEC: '#' wildcard)",
+                a.bindings, seed_of(a.bindings), "reference (COMPAT: '#' literal)" if a.mode == "compat" else "AMQP (SPEC: '#' wildcard)",
                 a.batch, N_BATCHES))
 
 
@@ -105,7 +116,7 @@ class ClockSampler:
 def make_table_inputs(a):
     from chanamq_b200.workload import TopicWorkload, queue_names_packed
 
-    w = TopicWorkload(SEED)
+    w = TopicWorkload(seed_of(a.bindings))
     pb, poff, q, d = w.patterns(a.bindings, a.bindings, hash_tail=True)
     qb, qoff = queue_names_packed(q)
     return w, (pb, poff, qb, qoff, d)
@@ -151,7 +162,7 @@ def run_reference(a, rank):
     sample = "%d keys per step x %d steps on %d threads (keys sharded over a read-only trie); trie build %.1f s not timed" % (
         n_keys, a.steps, threads, build_s)
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "impl": "reference", "metric": metric_name(a), "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": workload_name(a), "mean_queues_per_message": mbar},
@@ -317,12 +328,14 @@ def run_ours(a, rank, world, local_rank):
         except Exception:
             pass
         out = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "metric": metric_name(a), "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": dev_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u32", "data": "synthetic",
             "config": {"workload": workload_name(a), "mean_words_per_key": wbar, "mean_queues_per_message": mbar,
                        "sharding": "keys (table replicated per GPU, no data-path collective)",
-                       "l2": "10 distinct resident batches rotate; each step writes ~%.0f MB of ids (> 126 MB L2)" % (ids_per_batch * 4 / 1e6),
+                       "l2": "10 distinct resident batches rotate: %.0f MB of keys in all and ~%.0f MB of ids written per step, so "
+                             "a batch's keys have left the 126 MB L2 when its turn comes again (inputs larger than L2, no flush)" % (
+                                 sum(hb.numel() + 4 * ho.numel() for hb, ho in host) / 1e6, ids_per_batch * 4 / 1e6),
                        "table": {k: st[k] for k in ("bindings", "queues", "groups", "shapes", "words", "wstride", "table_bytes")},
                        "table_build_s": build_s,
                        "numa": {"node_rank0": numa_node.value, "cpus_rank0": numa_cpus.value} if not a.no_numa else None},
@@ -344,6 +357,8 @@ def run_ours(a, rank, world, local_rank):
         }
         if slices is not None:
             out["binding_slices"] = slices
+        if world == 1 and not a.no_configs:
+            out["configs"] = run_config_legs()
         if world == 1 and not a.no_cpu_baseline:
             rate, per_step, cbuild, cm, _, want = cpu_route_rate(a, w, binds, a.cpu_sample, 1, 1, 0, stream0=0)
             # parity of the timed path on the timed configuration: the oracle has just routed the first cpu_sample keys
@@ -370,6 +385,38 @@ def run_ours(a, rank, world, local_rank):
     if dist:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_config_legs():
+    """Short legs for the other BASELINE.json configs, each in its own process after the headline (the GPU is idle by
+    then): config 2 (100 k bindings, SPEC '#' semantics), config 3 (headers x-match), config 5 (decode -> route).  Every
+    leg checks a sample of its result against its oracle and exits non-zero on a mismatch (parity = it exited 0)."""
+    legs = {
+        "config2_topic_100k_spec": [os.path.join(ROOT, "bench.py"), "--bindings", "100000", "--mode", "spec", "--steps", "30",
+                                    "--warmup", "3", "--cpu-sample", "20000", "--no-configs"],
+        "config3_headers_50k": [os.path.join(ROOT, "bench_headers.py"), "--steps", "10", "--warmup", "3", "--cpu-sample", "300"],
+        "config5_decode_route_1gib": [os.path.join(ROOT, "bench_decode.py"), "--route", "--steps", "5", "--warmup", "3",
+                                      "--cpu-sample-bytes", str(64 << 20)],
+    }
+    out = {}
+    for name, cmd in legs.items():
+        t0 = time.perf_counter()
+        try:
+            r = subprocess.run([sys.executable] + cmd, capture_output=True, text=True, timeout=240)
+            lines = [ln for ln in r.stdout.strip().splitlines() if ln.startswith("{")]
+            if r.returncode != 0 or not lines:
+                out[name] = {"failed": (r.stderr.strip().splitlines() or ["exit %d" % r.returncode])[-1][:300]}
+                continue
+            d = json.loads(lines[-1])
+            par = d.get("parity", {})
+            out[name] = {"metric": d.get("metric"), "value": d.get("value"), "unit": d.get("unit"), "ms_per_step": d.get("ms_per_step"),
+                         "roofline_frac": (d.get("roofline") or {}).get("frac"), "e2e": (d.get("e2e") or {}).get("value"),
+                         "cpu_baseline": (d.get("cpu_baseline") or {}).get("value"),
+                         "parity": {"equal": par.get("equal", True), "checked": par.get("checked_keys", "sample asserted inside the leg")},
+                         "workload": (d.get("config") or {}).get("workload"), "leg_s": time.perf_counter() - t0}
+        except Exception as e:  # a leg must never take the headline line down with it
+            out[name] = {"failed": repr(e)[:300]}
+    return out
 
 
 def run_binding_slices(a, rank, world, local_rank, w, binds, mbar, dist, barrier):

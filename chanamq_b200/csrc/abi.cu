@@ -244,6 +244,7 @@ int upload_table(chq_table* t) {
 int enqueue_route(chq_table* t, Workspace& ws, const uint8_t* d_blob, const uint32_t* d_off, const uint32_t* d_klen, uint32_t n,
                   uint32_t* d_offsets, uint32_t* d_ids, uint64_t ids_cap, uint8_t* d_durable, uint8_t* d_err,
                   uint64_t* d_total, int32_t* d_status, cudaStream_t st) {
+  NvtxRange nvtx_range("chq: tokenize + route launches");
   const uint32_t n_tiles = route_scan_tiles(n);
   const bool headers = t->ct.headers_mode;  // d_blob/d_off/d_klen then describe the messages' headers tables
   int rc;
@@ -491,6 +492,7 @@ int patch_table(chq_table* t, const std::vector<Patch>& patches, bool* fits) {
 }
 
 int commit_impl(chq_table* t, bool allow_incremental) {
+  NvtxRange nvtx_range("chq_commit");
   std::lock_guard<std::mutex> g(t->mu);
   if (t->host_only) {  // no device copy: the same decision, host side only
     std::vector<Patch> patches;
@@ -568,6 +570,7 @@ int32_t chq_route_submit(chq_table* t, int32_t slot, const uint8_t* keys_blob, c
   if (!t->committed) return fail(CHQ_E_NOT_COMMITTED, "chq_route: table has uncommitted binds (call chq_commit)");
   int rc = set_device(t);
   if (rc) return rc;
+  NvtxRange nvtx_range("chq_route_submit (H2D + launches)");
   RouteSlot& s = t->slots[slot];
   if ((rc = slot_init(s))) return rc;
   if (s.busy) CU(cudaStreamSynchronize(s.st));
@@ -609,6 +612,7 @@ int32_t chq_route_submit(chq_table* t, int32_t slot, const uint8_t* keys_blob, c
 
 int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
   if (!t || slot < 0 || slot >= CHQ_SLOTS || !out) return fail(CHQ_E_ARG, "chq_route_wait: bad argument");
+  NvtxRange nvtx_range("chq_route_wait (D2H of the result)");
   RouteSlot& s = t->slots[slot];
   if (!s.busy) return fail(CHQ_E_ARG, "chq_route_wait: slot was not submitted");
   int rc = set_device(t);

@@ -9,7 +9,17 @@
 #define CHQ_ROUTE_SMALL 128
 #endif
 
+#include <nvtx3/nvToolsExt.h>   // header-only: ranges cost nothing unless a profiler is attached
+
 namespace chq {
+
+// NVTX range for the scope (tracing hooks of the shim) — nsys / ncu show submit, kernels and copies by name
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 constexpr int kRouteThreads = 128;   // messages per tile; one thread per message while probing
 constexpr int kRouteSlots = 8;       // matched groups remembered per message before the slow path

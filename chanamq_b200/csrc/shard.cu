@@ -341,6 +341,7 @@ int32_t chq_shard_route_device(chq_shard* s, const uint8_t* d_keys_blob, const u
     return sfail(CHQ_E_ARG, "chq_shard_route_device: bad argument");
   if (!s->max_keys) return sfail(CHQ_E_ARG, "chq_shard_route_device: call chq_shard_reserve first");
   if (n == 0 || n > s->max_keys) return sfail(CHQ_E_ARG, "chq_shard_route_device: 1 .. max_keys keys per batch (chq_shard_reserve)");
+  chq::NvtxRange nvtx_range("chq_shard_route_device (route, all-gather, pull, merge)");
   const NcclApi& nc = nccl();
   SCU(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;

@@ -17,7 +17,14 @@ def test_reference_arm_prints_one_contract_line():
     d = json.loads(lines[0])
     base = json.load(open(os.path.join(ROOT, "BASELINE.json")))
     assert d["impl"] == "reference" and d["unit"] == "msgs/s" and d["higher_is_better"] is True
-    assert d["metric"].split(" at ")[0] in base["metric"]
+    # the metric names the table it was measured on; at the default size it is BASELINE.json's
+    assert d["metric"] == "routed msgs/sec (topic, 2k bindings)"
+    sys.path.insert(0, ROOT)
+    import bench
+
+    class A:
+        bindings = 1_000_000
+    assert bench.metric_name(A) in base["metric"]
     for key in ("value", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
         assert key in d, key
     assert d["steps"] == 2 and d["warmup"] == 1 and d["value"] > 0 and d["vs_baseline"] is None
