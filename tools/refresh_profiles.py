@@ -12,11 +12,13 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 tag = sys.argv[1]
+rnd = sys.argv[2] if len(sys.argv) > 2 else "r02"   # prefix of the files written to profiles/
 src, dst = os.path.join(ROOT, "gpurun_out", tag), os.path.join(ROOT, "profiles")
-names = {"bench.json": "r01_bench_compat.json", "bench_ref.json": "r01_bench_reference_arm.json", "bench_spec.json": "r01_bench_spec.json",
-         "bench_headers.json": "r01_bench_headers.json", "bench_decode.json": "r01_bench_decode.json",
-         "bench_decode_one.json": "r01_bench_decode_one_segment.json", "bench_fanout.json": "r01_bench_fanout.json",
-         "launches.csv": "r01_launches.csv", "pytest_gpu.log": "r01_pytest_gpu.log"}
+names = {"bench.json": "bench_compat.json", "bench_ref.json": "bench_reference_arm.json", "bench_spec.json": "bench_spec.json",
+         "bench_headers.json": "bench_headers.json", "bench_decode.json": "bench_decode.json", "bench_encode.json": "bench_encode.json",
+         "bench_decode_one.json": "bench_decode_one_segment.json", "bench_fanout.json": "bench_fanout.json",
+         "launches.csv": "launches.csv", "pytest_gpu.log": "pytest_gpu.log"}
+names = {a: rnd + "_" + b for a, b in names.items()}
 for a, b in names.items():
     if os.path.exists(os.path.join(src, a)):
         shutil.copy(os.path.join(src, a), os.path.join(dst, b))
@@ -42,12 +44,12 @@ for k in ("write", "probe", "tokenize"):
     rep = os.path.join(src, "prof_%s.ncu-rep" % k)
     if not os.path.exists(rep):
         continue
-    with open(os.path.join(dst, "r01_k_%s_ncu_details.txt" % k), "w") as f:
+    with open(os.path.join(dst, rnd + "_k_%s_ncu_details.txt" % k), "w") as f:
         f.write(subprocess.run(["ncu", "-i", rep, "--page", "details"], capture_output=True, text=True).stdout)
     srcp = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
     tmp = "/tmp/src_%s.csv" % k
     open(tmp, "w").write(srcp)
-    with open(os.path.join(dst, "r01_k_%s_hot_lines.txt" % k), "w") as f:
+    with open(os.path.join(dst, rnd + "_k_%s_hot_lines.txt" % k), "w") as f:
         f.write(subprocess.run([sys.executable, os.path.join(dst, "ncu_lines.py"), tmp, "40"], capture_output=True, text=True).stdout)
     m = raw_metrics(rep)
     traffic["k_" + k] = {"dram_bytes_read": m.get("dram__bytes_read.sum"), "dram_bytes_write": m.get("dram__bytes_write.sum"),
@@ -62,9 +64,9 @@ if "k_write" in traffic and "k_probe" in traffic:
     offs = 8.4e6  # k_offsets is not captured: its algorithmic bytes (cnt in, offsets out)
     total = sum(traffic[k]["dram_bytes_read"] + traffic[k]["dram_bytes_write"] for k in ("k_write", "k_probe")) + offs
     tok = traffic.pop("k_tokenize", None)
-    json.dump({"what": "DRAM traffic of the route launch group (k_probe + k_offsets + k_write), per batch of 2^20 keys against the 1 M-binding "
+    json.dump({"what": "DRAM traffic of the route launch group (k_probe + k_offsets + k_write; k_write_rest finds an almost empty list on this workload), per batch of 2^20 keys against the 1 M-binding "
                        "table, from one `ncu --set full --clock-control none` capture of each kernel (gpurun_out/%s, summarised in "
-                       "profiles/r01_k_*_ncu_details.txt)" % tag,
+                       "profiles/%s_k_*_ncu_details.txt)" % (tag, rnd),
                "dram_bytes_per_launch": total, "algorithmic_bytes_per_launch": bench["roofline"]["algorithmic_bytes_per_launch"],
                "kernels": dict(traffic, k_offsets={"dram_bytes_read": offs / 2, "dram_bytes_write": offs / 2, "note": "not captured: algorithmic bytes"}),
                "k_tokenize": tok,
