@@ -17,6 +17,18 @@ struct __align__(16) KwayBuf {
   uint32_t start[kRouteSlots + 1];   // run r = [start[r], start[r + 1])
 };
 
+// number of a[0 .. n) below x; n is the same for all lanes, so every lane runs the same number of steps
+__device__ __forceinline__ uint32_t smem_lower_bound_uniform(const uint32_t* a, uint32_t n, uint32_t x) {
+  if (n == 0) return 0;
+  uint32_t base = 0;
+  while (n > 1) {
+    const uint32_t half = n >> 1;
+    if (a[base + half - 1] < x) base += half;
+    n -= half;
+  }
+  return base + (a[base] < x ? 1u : 0u);
+}
+
 // Lane j < k holds list j = qlist[my_off .. my_off + my_len), k <= kRouteSlots, total <= kKwayMax ids, no id in two
 // lists.  Writes the sorted union to out[0 .. total).
 __device__ __forceinline__ void warp_kway(const uint32_t* __restrict__ qlist, uint32_t my_off, uint32_t my_len, int k, KwayBuf& kb,
@@ -39,18 +51,20 @@ __device__ __forceinline__ void warp_kway(const uint32_t* __restrict__ qlist, ui
   uint32_t* A = kb.a;
   uint32_t* B = kb.b;
   for (int runs = k; runs > 1; runs = (runs + 1) >> 1) {
-    for (uint32_t e = lane; e < total; e += 32) {
-      int r = 0;   // the run of element e (at most eight boundaries)
-#pragma unroll
-      for (int j = 1; j < kRouteSlots; ++j) r += (j < runs && kb.start[j] <= e) ? 1 : 0;
-      const uint32_t x = A[e];
+    // run by run (all lanes on the same run: its partner, and with it the number of search steps, is the same for
+    // every lane): an element's place in the merged pair = its index + the partner's ids below it
+    for (int r = 0; r < runs; ++r) {
+      const uint32_t rs = kb.start[r], rl = kb.start[r + 1] - rs;
       const int p = r ^ 1;
-      uint32_t pos = e;   // a run without a partner keeps its place
       if (p < runs) {
-        const uint32_t ps = kb.start[p], pl = kb.start[p + 1] - ps;
-        pos = (e - kb.start[r]) + smem_lower_bound(A + ps, pl, x) + kb.start[r & ~1];   // (no ties: the lists share nothing)
+        const uint32_t ps = kb.start[p], pl = kb.start[p + 1] - ps, base = kb.start[r & ~1];
+        for (uint32_t i = lane; i < rl; i += 32) {
+          const uint32_t x = A[rs + i];
+          B[base + i + smem_lower_bound_uniform(A + ps, pl, x)] = x;   // (no ties: the lists share nothing)
+        }
+      } else {  // a run without a partner keeps its place
+        for (uint32_t i = lane; i < rl; i += 32) B[rs + i] = A[rs + i];
       }
-      B[pos] = x;
     }
     __syncwarp();
     // runs 2 j and 2 j + 1 became run j
