@@ -362,7 +362,7 @@ int32_t chq_profile(chq_table* t, int32_t enable, double* tokenize_ms, double* r
 int32_t chq_profile_kernels(chq_table* t, int32_t enable, double* kernel_ms, uint32_t* launches);
 /* how many of this library's kernels have been launched by this process (all tables) */
 uint64_t chq_kernel_launches(void);
-/* measurement hook: cycle totals of the write kernel by kind of message (32 counters: cycles, messages, ids per
+/* measurement hook: cycle totals of k_write_rest by kind of message (32 counters: cycles, messages, ids per
  * bin, see kernels.cu); all zero unless the library was built with -DCHQ_CLOCKS.  Reading resets them. */
 int32_t chq_debug_clocks(uint64_t* out32);
 /* test hook: structural invariants of the compiled table on the host (lists ascending and inside the table, ids in

@@ -1,4 +1,4 @@
-"""Cycle accounting of k_write by kind of message.  Needs a library built with CHQ_NVCC_DEFS=-DCHQ_CLOCKS:
+"""Cycle accounting of k_write_rest (the messages the main write kernel leaves out) by kind of message.  Needs a library built with CHQ_NVCC_DEFS=-DCHQ_CLOCKS:
    CHQ_NVCC_DEFS=-DCHQ_CLOCKS python -c "import __graft_entry__ as g; g.build()"; python tools/clocks.py [compat|spec]"""
 import ctypes as C, os, sys
 import numpy as np
