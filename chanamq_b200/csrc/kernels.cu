@@ -437,6 +437,11 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   // measured faster)
   else if (!dedup && k >= 4 && k <= p.max_slots && ub <= (uint32_t)kKwayMax && ub - mxlen >= 2u * mxlen && ub > 64u &&
            p.max_small == (uint32_t)kRouteSmall) { cls = 5; cnt = ub; }
+  // two lists of similar length that share nothing: a symmetric merge through registers (warp_merge2)
+  // (slices of a sharded exchange only: in a table such pairs are rare, and the few long ones, merged by one warp in
+  // dependent trips, set the run time of k_write_rest — measured: +0.005 ms on the headline batch)
+  else if (p.slice_offsets && !dedup && k == 2 && k <= p.max_slots && 2u * (ub - mxlen) >= mxlen && ub > 64u && ub < (1u << 30) &&
+           p.max_small == (uint32_t)kRouteSmall) { cls = 6; cnt = ub; }
   // (nothing shared between the lists: the flat path of k_write takes a much longer short side)
   else if (ub - mxlen > ((dedup || mxlen > (uint32_t)kFlatMaxLong || p.max_small != (uint32_t)kRouteSmall) ? p.max_small
                                                                                                              : (uint32_t)kFlatMaxShort) ||
@@ -616,6 +621,9 @@ __device__ __forceinline__ void write_message(const WriteCtx& p, WarpScratch& ws
   } else if (cl == 5) {
     if (lane >= kk) lo = ll = 0;
     warp_kway(p.qlist, lo, ll, kk, *p.kway, p.ids + o, lane);
+  } else if (cl == 6) {
+    warp_merge2(p.qlist, __shfl_sync(kFull, lo, 0), __shfl_sync(kFull, ll, 0), __shfl_sync(kFull, lo, 1), __shfl_sync(kFull, ll, 1),
+                p.ids + o, lane);
   } else if (kk == 1) {
     const uint32_t* sp = p.qlist + __shfl_sync(kFull, lo, 0) + lane;
     uint32_t* dst = p.ids + o + lane;

@@ -79,5 +79,31 @@ __device__ __forceinline__ void warp_kway(const uint32_t* __restrict__ qlist, ui
   for (uint32_t e = lane; e < total; e += 32) CHQ_ST_OUT(out + e, A[e]);
 }
 
+// Two lists of similar length that share nothing (two slices of a sharded exchange, two '#' patterns): a symmetric
+// merge through registers.  Both lists show a window of 32 ids, one per lane; everything up to T = the smaller of the
+// two windows' last ids (a list that ends inside its window sets no bound) can be placed for good: an id's place =
+// ids already written + its lane + the other window's ids below it (a shuffle binary search).  The list that sets T
+// empties its whole window, so a trip writes at least 32 ids, about 63 when the lists interleave evenly.
+__device__ __forceinline__ void warp_merge2(const uint32_t* __restrict__ qlist, uint32_t oa, uint32_t na, uint32_t ob, uint32_t nb,
+                                            uint32_t* __restrict__ out, int lane) {
+  uint32_t ia = 0, ib = 0;
+  const uint32_t* pa = qlist + oa + lane;
+  const uint32_t* pb = qlist + ob + lane;
+  while (ia < na || ib < nb) {
+    const uint32_t ra = na - ia, rb = nb - ib;
+    const uint32_t a = (uint32_t)lane < ra ? __ldg(pa + ia) : kNone;
+    const uint32_t b = (uint32_t)lane < rb ? __ldg(pb + ib) : kNone;
+    const uint32_t a31 = __shfl_sync(kFull, a, 31), b31 = __shfl_sync(kFull, b, 31);
+    const uint32_t T = min(ra > 32 ? a31 : kNone, rb > 32 ? b31 : kNone);
+    const bool ea = a != kNone && a <= T, eb = b != kNone && b <= T;   // prefixes of the lanes: the windows ascend
+    const uint32_t below_a = lanes_below(b, a), below_b = lanes_below(a, b);
+    uint32_t* o = out + (ia + ib + lane);
+    if (ea) CHQ_ST_OUT(o + below_a, a);
+    if (eb) CHQ_ST_OUT(o + below_b, b);
+    ia += __popc(__ballot_sync(kFull, ea));
+    ib += __popc(__ballot_sync(kFull, eb));
+  }
+}
+
 }  // namespace
 }  // namespace chq

@@ -103,7 +103,8 @@ def test_two_ranks_over_gloo_merge_to_the_unsharded_result():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("g,p,nq", [(2, 30_000, 30_000), (8, 60_000, 15_000), (4, 200_000, 50_000), (4, 200_000, 200_000)])
+@pytest.mark.parametrize("g,p,nq", [(2, 30_000, 30_000), (8, 60_000, 15_000), (4, 200_000, 50_000), (4, 200_000, 200_000),
+                                    (2, 400_000, 400_000), (8, 400_000, 400_000)])
 def test_slices_on_one_gpu_merge_to_the_unsharded_oracle(g, p, nq):
     """G slice tables on one device (what G ranks would hold), routed one after the other, merged by
     chq_merge_slices_device: must equal the oracle over the whole table (4 bindings per queue in two of the
@@ -121,7 +122,7 @@ def test_slices_on_one_gpu_merge_to_the_unsharded_oracle(g, p, nq):
     st = torch.cuda.current_stream().cuda_stream
     d_blob = torch.from_numpy(blob.copy()).to(dev)
     d_off = torch.from_numpy(off.view(np.int32).copy()).to(dev)
-    cap = 2_000_000
+    cap = 4_000_000
     all_off = torch.empty(g * (n + 1), dtype=torch.int32, device=dev)
     all_ids = torch.zeros(g * cap, dtype=torch.int32, device=dev)
     all_dur = torch.empty(g * n, dtype=torch.uint8, device=dev)
@@ -139,12 +140,12 @@ def test_slices_on_one_gpu_merge_to_the_unsharded_oracle(g, p, nq):
                        cap, all_dur.data_ptr() + r * n, err.data_ptr(), tot.data_ptr() + 16 * r, tot.data_ptr() + 16 * r + 8, st)
         tables.append(m)
     out_off = torch.empty(n + 1, dtype=torch.int32, device=dev)
-    out_ids = torch.empty(3_000_000, dtype=torch.int32, device=dev)
+    out_ids = torch.empty(6_000_000, dtype=torch.int32, device=dev)
     out_dur = torch.empty(n, dtype=torch.uint8, device=dev)
     # one queue per binding (nq == p): no queue sits in two slices, the merge may skip the de-duplication
     flags = 1 if nq == p else 0
     check(L.chq_merge_slices_device2(0, all_off.data_ptr(), all_ids.data_ptr(), cap, all_dur.data_ptr(), g, n, out_off.data_ptr(),
-                                     out_ids.data_ptr(), 3_000_000, out_dur.data_ptr(), tot.data_ptr() + 16 * g,
+                                     out_ids.data_ptr(), 6_000_000, out_dur.data_ptr(), tot.data_ptr() + 16 * g,
                                      tot.data_ptr() + 16 * g + 8, flags, st))
     torch.cuda.synchronize()
     t = tot.cpu().numpy()
