@@ -6,8 +6,11 @@
 // (chq_declare_queues), so ids agree across slices.  Per batch, on every rank, all on the caller's stream:
 //   1. the local route: ALL keys against this rank's slice (chq_route_device) -> slice CSR in a buffer the other
 //      ranks can read (cudaIpc);
-//   2. ncclAllGather of the slice offsets (+ status word) and of the durable flags over NVLink — the small arrays;
-//      the collective is also what orders step 3 behind every rank's step 1;
+//   2. the small arrays over NCCL / NVLink, in one group: every rank sends every owner the slice offsets and durable
+//      flags of that owner's message range (ncclSend / ncclRecv: 1/G of what an all-gather of the whole arrays would
+//      move to every rank — at 8 GPUs that was 42 MB per rank and step, 0.2 ms), and the status words are
+//      all-gathered; the collective is also what orders step 3 behind every rank's step 1.  CHQ_SHARD_ALLGATHER=1
+//      selects the plain ncclAllGather of the whole arrays instead;
 //   3. k_pull: rank g owns the messages [g n / G, (g+1) n / G).  It fetches, from every slice, just the ids of its
 //      own range: plain coalesced loads from the peers' buffers over NVLink into local memory (each id crosses NVLink
 //      once, nothing is padded, no size goes through the host), and rebases the offsets;
@@ -22,6 +25,7 @@
 #include <nccl.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -48,6 +52,8 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*GroupStart)() = nullptr;
   ncclResult_t (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -67,6 +73,8 @@ const NcclApi& nccl() {
     a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(sym("ncclCommInitRank"));
     a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(sym("ncclCommDestroy"));
     a.AllGather = reinterpret_cast<decltype(a.AllGather)>(sym("ncclAllGather"));
+    a.Send = reinterpret_cast<decltype(a.Send)>(sym("ncclSend"));
+    a.Recv = reinterpret_cast<decltype(a.Recv)>(sym("ncclRecv"));
     a.GroupStart = reinterpret_cast<decltype(a.GroupStart)>(sym("ncclGroupStart"));
     a.GroupEnd = reinterpret_cast<decltype(a.GroupEnd)>(sym("ncclGroupEnd"));
     a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
@@ -104,6 +112,8 @@ struct chq_shard {
   uint32_t* got = nullptr;                            // [G][pull_cap] the ids of this rank's range, slice by slice
   uint64_t* local_total = nullptr;                    // [2]: total, status of the local route
   int32_t* pull_status = nullptr;
+  int32_t* statuses = nullptr;                        // [G] gathered status words of the local routes
+  bool whole_arrays = false;                          // CHQ_SHARD_ALLGATHER=1: all-gather the whole small arrays
   const uint32_t** d_peer_ids = nullptr;              // device copy of peer_ids [2][kMaxWorld]
   unsigned batch = 0;
   // stage timing (chq_shard_stage_ms): events around the four stages of the last kStageRing batches
@@ -124,18 +134,20 @@ namespace {
 // Rank g's part of step 3 (see the head of the file), one grid row per slice r: the ids of the messages [m0, m1)
 // from slice r's result (a peer's memory for r != g: plain loads over NVLink) into got[r][...], that slice's offsets
 // rebased to the range, its durable flags, and the status words of all local routes folded into *status.
+// Slice r's offsets of the range are all_off[r * off_stride + first + 0 .. nn], its durable flags all_dur[r * dur_stride +
+// first + 0 .. nn) (first = 0 when only the ranges were exchanged, = the range's first message after a whole all-gather).
 __global__ void __launch_bounds__(256) k_pull(const uint32_t* __restrict__ all_off, size_t off_stride,
-                                              const uint8_t* __restrict__ all_dur, size_t dur_stride, uint32_t n, uint32_t m0,
-                                              uint32_t m1, const uint32_t* const* __restrict__ peer_ids, uint32_t* __restrict__ got,
-                                              uint64_t pull_cap, uint32_t* __restrict__ sub_off, uint8_t* __restrict__ sub_dur,
-                                              int32_t* __restrict__ status) {
-  const uint32_t r = blockIdx.y, nn = m1 - m0;
+                                              const uint8_t* __restrict__ all_dur, size_t dur_stride, uint32_t first, uint32_t nn,
+                                              const int32_t* __restrict__ statuses, const uint32_t* const* __restrict__ peer_ids,
+                                              uint32_t* __restrict__ got, uint64_t pull_cap, uint32_t* __restrict__ sub_off,
+                                              uint8_t* __restrict__ sub_dur, int32_t* __restrict__ status) {
+  const uint32_t r = blockIdx.y, m0 = first;
   const uint32_t* so = all_off + (size_t)r * off_stride;
-  const uint32_t a = so[m0], b = so[m1];
+  const uint32_t a = so[m0], b = so[m0 + nn];
   const uint64_t len = b - a, take = len < pull_cap ? len : pull_cap;
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
   if (tid == 0) {
-    const int32_t st = (int32_t)so[n + 1];             // slice r's local route: CHQ_OK, CHQ_E_OVERFLOW, CHQ_E_SCRATCH
+    const int32_t st = statuses[r];                    // slice r's local route: CHQ_OK, CHQ_E_OVERFLOW, CHQ_E_SCRATCH
     if (st != CHQ_OK) atomicMin(status, st);
     if (len > pull_cap) atomicMin(status, (int32_t)CHQ_E_OVERFLOW);
   }
@@ -187,7 +199,8 @@ void shard_release(chq_shard* s) {
     if (s->loc[b]) { cudaFree(s->loc[b]); s->loc[b] = nullptr; }
   }
   cudaFree(s->all_off); cudaFree(s->all_dur); cudaFree(s->sub_off); cudaFree(s->sub_dur); cudaFree(s->got);
-  cudaFree(s->local_total); cudaFree(s->pull_status); cudaFree(s->d_peer_ids);
+  cudaFree(s->local_total); cudaFree(s->pull_status); cudaFree(s->d_peer_ids); cudaFree(s->statuses);
+  s->statuses = nullptr;
   for (auto& e : s->ev) for (auto& x : e) if (x) { cudaEventDestroy(x); x = nullptr; }
   s->ev_n = 0;
   s->all_off = s->sub_off = s->got = nullptr;
@@ -299,6 +312,8 @@ int32_t chq_shard_reserve(chq_shard* s, uint32_t max_keys, uint64_t slice_cap, u
   SCU(cudaMalloc(&s->got, (size_t)G * pull_cap * 4 + 256));
   SCU(cudaMalloc(&s->local_total, 2 * sizeof(uint64_t)));
   SCU(cudaMalloc(&s->pull_status, sizeof(int32_t)));
+  SCU(cudaMalloc(&s->statuses, sizeof(int32_t) * kMaxWorld));
+  { const char* e = getenv("CHQ_SHARD_ALLGATHER"); s->whole_arrays = e && atoi(e) != 0; }
   SCU(cudaMalloc(&s->d_peer_ids, sizeof(uint32_t*) * 2 * kMaxWorld));
   // every rank learns where the others keep their slice results: the cudaIpc handles of both buffers, and the sizes
   // they were reserved with (which must agree), travel by one all-gather
@@ -362,18 +377,39 @@ int32_t chq_shard_route_device(chq_shard* s, const uint8_t* d_keys_blob, const u
                             s->local_total, reinterpret_cast<int32_t*>(lo + n + 1), st);
   if (rc) { g_shard_err = chq_last_error(); return rc; }
   if (pe) SCU(cudaEventRecord(pe[1], st));
-  // 2. the small arrays of every slice, to every rank
+  // 2. the small arrays: every owner gets its range of every slice's offsets and durable flags (or, on request,
+  //    everybody gets everything), and everybody gets every status word
+  size_t off_stride, dur_stride;
+  uint32_t first;
   SNC(nc.GroupStart());
-  SNC(nc.AllGather(lo, s->all_off, (size_t)n + 2, ncclUint32, s->comm, st));
-  SNC(nc.AllGather(s->loc_dur(b), s->all_dur, (size_t)n, ncclUint8, s->comm, st));
+  SNC(nc.AllGather(lo + n + 1, s->statuses, 1, ncclInt32, s->comm, st));
+  if (s->whole_arrays) {
+    SNC(nc.AllGather(lo, s->all_off, (size_t)n + 2, ncclUint32, s->comm, st));
+    SNC(nc.AllGather(s->loc_dur(b), s->all_dur, (size_t)n, ncclUint8, s->comm, st));
+    off_stride = (size_t)n + 2; dur_stride = n; first = m0;
+  } else {
+    off_stride = (size_t)nn + 1; dur_stride = nn; first = 0;
+    for (int g = 0; g < G; ++g) {
+      if (g == s->rank) continue;
+      const uint32_t g0 = (uint32_t)(((uint64_t)g * n) / G), g1 = (uint32_t)(((uint64_t)(g + 1) * n) / G);
+      SNC(nc.Send(lo + g0, (size_t)(g1 - g0) + 1, ncclUint32, g, s->comm, st));
+      SNC(nc.Recv(s->all_off + (size_t)g * off_stride, (size_t)nn + 1, ncclUint32, g, s->comm, st));
+      if (g1 > g0) SNC(nc.Send(s->loc_dur(b) + g0, (size_t)(g1 - g0), ncclUint8, g, s->comm, st));
+      if (nn) SNC(nc.Recv(s->all_dur + (size_t)g * dur_stride, (size_t)nn, ncclUint8, g, s->comm, st));
+    }
+  }
   SNC(nc.GroupEnd());
+  if (!s->whole_arrays) {  // this rank's own slice of its own range
+    SCU(cudaMemcpyAsync(s->all_off + (size_t)s->rank * off_stride, lo + m0, ((size_t)nn + 1) * 4, cudaMemcpyDeviceToDevice, st));
+    if (nn) SCU(cudaMemcpyAsync(s->all_dur + (size_t)s->rank * dur_stride, s->loc_dur(b) + m0, nn, cudaMemcpyDeviceToDevice, st));
+  }
   if (pe) SCU(cudaEventRecord(pe[2], st));
   // 3. the ids of this rank's message range from every slice (peers: over NVLink), offsets rebased
   SCU(cudaMemsetAsync(s->pull_status, 0, sizeof(int32_t), st));
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
   const unsigned rows = (unsigned)G, cols = (unsigned)((sms * 8 + G - 1) / G);
-  k_pull<<<dim3(cols, rows), 256, 0, st>>>(s->all_off, (size_t)n + 2, s->all_dur, (size_t)n, n, m0, m1,
+  k_pull<<<dim3(cols, rows), 256, 0, st>>>(s->all_off, off_stride, s->all_dur, dur_stride, first, nn, s->statuses,
                                            s->d_peer_ids + (size_t)b * kMaxWorld, s->got, s->pull_cap, s->sub_off, s->sub_dur,
                                            s->pull_status);
   chq::note_launches(1);
