@@ -498,10 +498,11 @@ def run_binding_slices(a, rank, world, local_rank, w, binds, mbar, dist, barrier
     ms = float(t[0])
     ex.close()
     return {"value": n * a.steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / a.steps, "status_ok": float(t[1]) == 0.0,
-            "what": "bindings sliced i mod G; every GPU routes all %d keys of a step against its slice; ncclAllGather of the slices' "
-                    "offsets and durable flags; each GPU pulls the ids of its own n/G messages from the peers' buffers over NVLink "
+            "what": "bindings sliced i mod G; every GPU routes all %d keys of a step against its slice; every owner receives its "
+                    "message range of every slice's offsets and durable flags over NCCL (CHQ_SHARD_ALLGATHER=1: the whole "
+                    "arrays, all-gathered); each GPU pulls the ids of its own n/G messages from the peers' buffers over NVLink "
                     "and merges them (chq_shard_route_device)" % n,
-            "nccl_bytes_received_per_rank_per_step": int(world * ((n + 2) * 4 + n)),
+            "nccl_bytes_received_per_rank_per_step": int((world - 1) * ((n // world + 1) * 4 + n // world) + 4 * world),
             "peer_bytes_pulled_per_rank_per_step": int(4 * mbar * n / world * (world - 1) / world),
             "setup_s": build_s, "parity": parity,
             "stage_ms_rank0": {k: v / max(1, stage_n) for k, v in stages.items()}}
