@@ -180,7 +180,7 @@ def run_ours(a, rank, world, local_rank):
     import torch
 
     from chanamq_b200 import CHQ_MODE_COMPAT, CHQ_MODE_SPEC, CHQ_TOPIC, GpuMatcher
-    from chanamq_b200._lib import load_library
+    from chanamq_b200._lib import CHQ_IDS_U24, CHQ_IDS_U32, load_library
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
@@ -294,6 +294,17 @@ def run_ours(a, rank, world, local_rank):
     chk = e2e_run(a.steps, a.warmup)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    # the same calls with the ids delivered as 3-byte values (chq_set_ids_format: optional, tables below 2^24 queues)
+    m.set_ids_format(CHQ_IDS_U24)
+    e2e_run(depth, 0)
+    barrier()
+    t0 = time.perf_counter()
+    chk24 = e2e_run(a.steps, a.warmup)
+    torch.cuda.synchronize()
+    e2e24_s = time.perf_counter() - t0
+    m.set_ids_format(CHQ_IDS_U32)
+    if chk24 != chk:
+        raise SystemExit("bench.py: the packed result counts %d ids, the uint32 one %d" % (chk24, chk))
     clocks = sampler.stop()  # sampled from the start of the device-timed region to the end of the end-to-end one
     clocks["window"] = "device-resident + end-to-end timed regions"
     h2d = int(np.mean([hb.numel() + ho.numel() * 4 for hb, ho in host]))
@@ -301,10 +312,10 @@ def run_ours(a, rank, world, local_rank):
 
     slices = run_binding_slices(a, rank, world, local_rank, w, binds, mbar, dist, barrier) if world > 1 else None
 
-    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    t = torch.tensor([dev_ms, e2e_s * 1e3, e2e24_s * 1e3], dtype=torch.float64, device=dev)
     if dist:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    dev_ms, e2e_ms, e2e24_ms = float(t[0]), float(t[1]), float(t[2])
     value = world * n * a.steps / (dev_ms * 1e-3)
     e2e_value = world * n * a.steps / (e2e_ms * 1e-3)
 
@@ -342,6 +353,10 @@ def run_ours(a, rank, world, local_rank):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / a.steps, "pipeline_depth": depth, "checksum_ids": chk,
                     "timing": "host wall clock around K pipelined chq_route_submit/chq_route_wait calls, pinned host keys in, host CSR out"},
+            "e2e_ids_u24": {"value": world * n * a.steps / (e2e24_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e24_ms / a.steps,
+                            "d2h_bytes_per_step": int((n + 1) * 4 + 2 * n + 16 + ids_per_batch * 3),
+                            "what": "the e2e calls with chq_set_ids_format(CHQ_IDS_U24): queue ids reach the host as 3-byte "
+                                    "values (one more kernel, k_pack24, per batch); optional, `e2e` above is the uint32 form"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks, "unit": "GB/s", "frac": achieved / peaks,

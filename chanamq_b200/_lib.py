@@ -13,6 +13,7 @@ CHQ_MODE_COMPAT, CHQ_MODE_SPEC = 0, 1
 CHQ_OK, CHQ_E_ZERO_WORDS, CHQ_E_KEY_TOO_LONG, CHQ_E_OVERFLOW, CHQ_E_CUDA, CHQ_E_ARG, CHQ_E_NOT_COMMITTED, CHQ_E_SCRATCH = (
     0, -1, -2, -3, -4, -5, -6, -7)
 CHQ_SLOTS = 4
+CHQ_IDS_U32, CHQ_IDS_U24 = 0, 1
 
 
 class ChqError(RuntimeError):
@@ -23,7 +24,7 @@ class ChqError(RuntimeError):
 
 class ChqResult(C.Structure):
     _fields_ = [("n", C.c_uint32), ("offsets", C.c_void_p), ("queue_ids", C.c_void_p), ("any_durable", C.c_void_p),
-                ("err", C.c_void_p)]
+                ("err", C.c_void_p), ("ids_format", C.c_int32)]
 
 
 _lib = None
@@ -60,6 +61,8 @@ def load_library():
         "chq_route": (i32, [vp, vp, vp, u32, vp, vp, C.POINTER(ChqResult)]),
         "chq_route_submit": (i32, [vp, i32, vp, vp, u32]),
         "chq_route_wait": (i32, [vp, i32, C.POINTER(ChqResult)]),
+        "chq_set_ids_format": (i32, [vp, i32]),
+        "chq_unpack_u24": (None, [vp, u64, vp]),
         "chq_route_device": (i32, [vp, vp, vp, u32, vp, vp, u64, vp, vp, vp, vp, vp]),
         "chq_route_device_static": (i32, [vp, vp, vp, u32, vp, vp, u64, vp, vp, vp, vp, vp]),
         "chq_declare_queues": (i32, [vp, vp, vp, u32]),

@@ -22,7 +22,7 @@ def _newer(target, sources):
 
 def build_product(force=False, verbose=False):
     out = os.path.join(HERE, "libchanagpu.so")
-    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "abi.cu", "decode.cu", "headers.cu", "fanout.cu", "encode.cu", "shard.cu", "host_table.cpp", "host_headers.cpp", "host_inc.cpp", "numa.cpp")]
+    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "abi.cu", "decode.cu", "headers.cu", "fanout.cu", "encode.cu", "shard.cu", "pack.cu", "host_table.cpp", "host_headers.cpp", "host_inc.cpp", "numa.cpp")]
     deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "chanamq_gpu.h")]
     force = force or bool(os.environ.get("CHQ_NVCC_DEFS", "").strip())  # experiment builds never reuse a library
     if not force and not _newer(out, deps):

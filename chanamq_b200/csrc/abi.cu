@@ -115,6 +115,8 @@ struct RouteSlot {
   DevBuf<uint8_t> d_blob;
   DevBuf<uint32_t> d_off;
   DevBuf<uint32_t> d_offsets, d_ids;
+  DevBuf<uint32_t> d_packed;  // CHQ_IDS_U24: the ids as 3-byte values (pack.cu), what the host gets instead of d_ids
+  int32_t ids_format = CHQ_IDS_U32;  // of the batch in flight
   DevBuf<uint8_t> d_durable, d_err;
   DevBuf<uint64_t> d_total;   // [0] total, [1] status (as int32 in low word)
   PinBuf<uint32_t> r_offsets, r_ids;
@@ -125,7 +127,7 @@ struct RouteSlot {
   bool busy = false;
   void release() {
     ws.release(); h_blob.release(); h_off.release(); d_blob.release(); d_off.release(); d_offsets.release();
-    d_ids.release(); d_durable.release(); d_err.release(); d_total.release(); r_offsets.release();
+    d_ids.release(); d_packed.release(); d_durable.release(); d_err.release(); d_total.release(); r_offsets.release();
     r_ids.release(); r_durable.release(); r_err.release(); r_total.release();
     if (meta_done) cudaEventDestroy(meta_done);
     if (st) cudaStreamDestroy(st);
@@ -164,6 +166,7 @@ struct chq_table {
   RouteSlot slots[CHQ_SLOTS];
   Workspace dev_ws;  // for chq_route_device
   uint32_t max_slots = kRouteSlots, max_small = kRouteSmall;
+  std::atomic<int32_t> ids_format{CHQ_IDS_U32};  // host results of chq_route / chq_route_wait (chq_set_ids_format)
   bool profile = false;
   uint64_t n_batches = 0, n_messages = 0, n_ids = 0;
   std::mutex mu;  // bind may arrive from a Future callback off the actor thread (ExchangeEntity.scala:337-338)
@@ -338,6 +341,10 @@ int slot_launch(chq_table* t, RouteSlot& s) {
   int rc = enqueue_route(t, s.ws, s.d_blob.p, s.d_off.p, nullptr, s.n, s.d_offsets.p, s.d_ids.p, s.d_ids.cap, s.d_durable.p,
                          s.d_err.p, s.d_total.p, reinterpret_cast<int32_t*>(s.d_total.p + 1), s.st);
   if (rc) return rc;
+  if (s.ids_format == CHQ_IDS_U24) {
+    if ((rc = s.d_packed.ensure(3 * (s.d_ids.cap / 4 + 1)))) return rc;
+    CU(launch_pack24(s.d_ids.p, s.d_total.p, s.d_ids.cap, s.d_packed.p, t->n_sms, s.st));
+  }
   CU(cudaMemcpyAsync(s.r_total.p, s.d_total.p, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.st));
   CU(cudaMemcpyAsync(s.r_offsets.p, s.d_offsets.p, ((size_t)s.n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.st));
   if (s.n) {
@@ -575,6 +582,9 @@ int32_t chq_route_submit(chq_table* t, int32_t slot, const uint8_t* keys_blob, c
   if ((rc = slot_init(s))) return rc;
   if (s.busy) CU(cudaStreamSynchronize(s.st));
   s.n = n;
+  s.ids_format = t->ids_format.load();
+  if (s.ids_format == CHQ_IDS_U24 && t->ct.queue_names.size() >= (1u << 24))
+    return fail(CHQ_E_ARG, "chq_route: CHQ_IDS_U24 needs a table of fewer than 2^24 queues");
   const size_t blob_len = n ? key_offsets[n] : 0;
   if ((rc = s.d_blob.ensure(blob_len + 16))) return rc;
   if ((rc = s.d_off.ensure((size_t)n + 1))) return rc;
@@ -642,8 +652,11 @@ int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
     if ((rc = slot_launch(t, s))) return rc;
   }
   const uint64_t total = s.r_total.p[0];
-  if ((rc = s.r_ids.ensure(total + 1))) return rc;
-  if (total) CU(cudaMemcpyAsync(s.r_ids.p, s.d_ids.p, total * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.st));
+  // (CHQ_IDS_U24: 3 bytes per id, the copy rounded up to whole words — the packed array is padded with zeros)
+  const bool u24 = s.ids_format == CHQ_IDS_U24;
+  const uint64_t id_words = u24 ? (3 * total + 3) / 4 : total;
+  if ((rc = s.r_ids.ensure(id_words + 1))) return rc;
+  if (total) CU(cudaMemcpyAsync(s.r_ids.p, u24 ? s.d_packed.p : s.d_ids.p, id_words * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.st));
   CU(cudaStreamSynchronize(s.st));
   s.busy = false;
   s.last_total = total;
@@ -651,9 +664,20 @@ int32_t chq_route_wait(chq_table* t, int32_t slot, chq_result* out) {
   out->n = s.n;
   out->offsets = s.r_offsets.p;
   out->queue_ids = s.r_ids.p;
+  out->ids_format = s.ids_format;
   out->any_durable = s.r_durable.p;
   out->err = s.r_err.p;
   return CHQ_OK;
+}
+
+int32_t chq_set_ids_format(chq_table* t, int32_t format) {
+  if (!t || (format != CHQ_IDS_U32 && format != CHQ_IDS_U24)) return fail(CHQ_E_ARG, "chq_set_ids_format: bad argument");
+  t->ids_format.store(format);  // batches already submitted keep the format they were submitted with
+  return CHQ_OK;
+}
+
+void chq_unpack_u24(const uint8_t* packed, uint64_t n_ids, uint32_t* out) {
+  for (uint64_t j = 0; j < n_ids; ++j, packed += 3) out[j] = (uint32_t)packed[0] | ((uint32_t)packed[1] << 8) | ((uint32_t)packed[2] << 16);
 }
 
 int32_t chq_route(chq_table* t, const uint8_t* keys_blob, const uint32_t* key_offsets, uint32_t n,

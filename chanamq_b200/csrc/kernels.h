@@ -83,6 +83,9 @@ cudaError_t launch_headers_match(const uint8_t* blob, const uint32_t* off, const
 // between: optional three events, recorded after k_probe, k_offsets and k_write (per-kernel timing)
 cudaError_t launch_route(const RouteParams& p, int n_sms, cudaStream_t st, cudaEvent_t* between = nullptr);
 cudaError_t launch_finish(const uint32_t* ctrl, int32_t* d_status, cudaStream_t st);
+// pack.cu: the ids of a finished batch as 3-byte values (total_status = the launch's {ids, status} pair on the device)
+cudaError_t launch_pack24(const uint32_t* ids, const uint64_t* total_status, uint64_t ids_cap, uint32_t* out, int n_sms,
+                          cudaStream_t st);
 unsigned long long kernel_launches();
 cudaError_t read_clocks(unsigned long long* out32);
 

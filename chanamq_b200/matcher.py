@@ -195,9 +195,23 @@ class GpuMatcher:
         n = res.n
         off = _view(res.offsets, n + 1, np.uint32)
         total = int(off[n]) if n else 0
-        out = RouteResult(off, _view(res.queue_ids, total, np.uint32), _view(res.any_durable, n, np.uint8),
-                          _view(res.err, n, np.uint8))
+        if res.ids_format == _lib.CHQ_IDS_U24:  # packed 3-byte ids (chq_set_ids_format): uint8[3 * total]
+            ids = _view(res.queue_ids, 3 * total, np.uint8)
+        else:
+            ids = _view(res.queue_ids, total, np.uint32)
+        out = RouteResult(off, ids, _view(res.any_durable, n, np.uint8), _view(res.err, n, np.uint8))
         return RouteResult(*[a.copy() for a in out]) if copy else out
+
+    def set_ids_format(self, fmt):
+        """CHQ_IDS_U24: host results carry the queue ids as 3-byte little-endian values (RouteResult.queue_ids is
+        then uint8[3 * total]; unpack_u24 expands it)."""
+        check(self.L.chq_set_ids_format(self.h, fmt))
+
+    def unpack_u24(self, packed):
+        packed = np.ascontiguousarray(packed, dtype=np.uint8)
+        out = np.empty(len(packed) // 3, dtype=np.uint32)
+        self.L.chq_unpack_u24(packed.ctypes.data, len(out), out.ctypes.data)
+        return out
 
     def route_packed(self, blob, off, copy=True):
         """blob uint8[], off uint32[n+1] (host) -> RouteResult (views into library memory unless copy)"""

@@ -106,10 +106,25 @@ int32_t chq_queue_name(const chq_table* t, uint32_t queue_id, const uint8_t** na
 typedef struct {
   uint32_t n;
   const uint32_t* offsets;   /* n+1 */
-  const uint32_t* queue_ids; /* offsets[n] */
+  const uint32_t* queue_ids; /* offsets[n]; with CHQ_IDS_U24 the same ids as 3-byte values, see chq_set_ids_format */
   const uint8_t* any_durable; /* n */
   const uint8_t* err;        /* n */
+  int32_t ids_format;        /* CHQ_IDS_U32 or CHQ_IDS_U24: how queue_ids is laid out */
 } chq_result;
+
+/* ---- a smaller host result (no counterpart in the reference: the JVM path never moves a result between memories).
+ *      End to end, chq_route is the device->host copy of the queue ids and nothing else.  A table with
+ *      fewer than 2^24 queues may ask for them as 3 bytes each, little-endian, back to back — a quarter less to
+ *      copy: with b = (const uint8_t*)result.queue_ids, id j of the batch is b[3j] | b[3j+1] << 8 | b[3j+2] << 16,
+ *      and message i's ids are j in [offsets[i], offsets[i+1]) as before.  The array is padded with zero bytes to a
+ *      multiple of 4.  Applies to chq_route / chq_route_submit + chq_route_wait (host results) only; the device
+ *      entry points always write uint32.  A batch submitted while the table has 2^24 queues or more is refused
+ *      (CHQ_E_ARG).  chq_unpack_u24 expands n_ids packed ids into uint32 on the host (plain C loop; a consumer
+ *      that walks the ids once reads them in place instead). ---- */
+#define CHQ_IDS_U32 0
+#define CHQ_IDS_U24 1
+int32_t chq_set_ids_format(chq_table* t, int32_t format);
+void chq_unpack_u24(const uint8_t* packed, uint64_t n_ids, uint32_t* out);
 
 /* Host buffers in, host result out (H2D, kernels, D2H inside).  keys_blob / key_offsets may be
  * ordinary or pinned host memory; pinned (chq_host_alloc) skips one staging copy.

@@ -219,6 +219,34 @@ def test_pipelined_slots_match_the_blocking_call():
         assert all(np.array_equal(a, b) for a, b in zip(want[i], got[i])), i
 
 
+def test_ids_as_three_bytes_equal_the_uint32_result():  # chq_set_ids_format(CHQ_IDS_U24), pack.cu
+    import torch
+    from chanamq_b200._lib import CHQ_IDS_U24, CHQ_IDS_U32
+    w, m, o = _load_workload(2, 100_000, 100_000, CHQ_MODE_COMPAT, True)  # queue ids up to 99 999: all three bytes in use
+    for n_keys in (0, 1, 7, 5_000, 60_001):
+        blob, off = w.keys(n_keys, stream=5)
+        m.set_ids_format(CHQ_IDS_U32)
+        want = assert_same_routing(m, o, blob, off, threads=4) if n_keys else m.route_packed(blob, off)
+        m.set_ids_format(CHQ_IDS_U24)
+        for _ in range(2):  # twice: the second batch reuses the slot's buffers
+            got = m.route_packed(blob, off)
+            assert got.queue_ids.dtype == np.uint8 and len(got.queue_ids) == 3 * len(want.queue_ids)
+            assert np.array_equal(got.offsets, want.offsets) and np.array_equal(got.err, want.err)
+            assert np.array_equal(got.any_durable, want.any_durable)
+            assert np.array_equal(m.unpack_u24(got.queue_ids), want.queue_ids)
+        # pipelined slots keep the format they were submitted with
+        hb = torch.from_numpy(np.concatenate([blob, np.zeros(1, np.uint8)])).pin_memory()
+        ho = torch.from_numpy(off.view(np.int32).copy()).pin_memory()
+        m.submit(0, hb.data_ptr(), ho.data_ptr(), n_keys)
+        m.set_ids_format(CHQ_IDS_U32)
+        m.submit(1, hb.data_ptr(), ho.data_ptr(), n_keys)
+        r0, r1 = m.wait(0, copy=True), m.wait(1, copy=True)
+        assert r0.queue_ids.dtype == np.uint8 and np.array_equal(m.unpack_u24(r0.queue_ids), want.queue_ids)
+        assert r1.queue_ids.dtype == np.uint32 and np.array_equal(r1.queue_ids, want.queue_ids)
+    assert int(want.queue_ids.max()) >= 1 << 16
+    m.close()
+
+
 def test_device_entry_point_with_torch_buffers():
     torch = pytest.importorskip("torch")
     w, m, o = _load_workload(2, 50_000, 50_000, CHQ_MODE_SPEC, True)
