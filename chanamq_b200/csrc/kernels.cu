@@ -433,10 +433,11 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   // one long list + at most max_small other ids: k_write's staged weave (weave.cuh); more: warp_union_long
   // lists of similar length that share nothing (the slices of a sharded exchange, several '#' patterns): staged and
   // merged pairwise in shared memory (kway.cuh)
-  // (from four lists on, none of which dominates: otherwise streaming the longest and placing the others was
-  // measured faster)
-  else if (!dedup && k >= 4 && k <= p.max_slots && ub <= (uint32_t)kKwayMax && ub - mxlen >= 2u * mxlen && ub > 64u &&
-           p.max_small == (uint32_t)kRouteSmall) { cls = 5; cnt = ub; }
+  // (in a table: from four lists on, none of which dominates — otherwise streaming the longest and placing the others
+  // was measured faster; the slices of a sharded exchange: from three slices on always — placing means k - 1 searches
+  // in global memory per id there, and set the run time of k_write)
+  else if (!dedup && k <= p.max_slots && ub <= (uint32_t)kKwayMax && p.max_small == (uint32_t)kRouteSmall &&
+           (p.slice_offsets ? k >= 3 : (k >= 4 && ub - mxlen >= 2u * mxlen && ub > 64u))) { cls = 5; cnt = ub; }
   // two lists of similar length that share nothing: a symmetric merge through registers (warp_merge2)
   // (slices of a sharded exchange only: in a table such pairs are rare, and the few long ones, merged by one warp in
   // dependent trips, set the run time of k_write_rest — measured: +0.005 ms on the headline batch)

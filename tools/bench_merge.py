@@ -79,3 +79,7 @@ e1.record()
 torch.cuda.synchronize()
 print("G=%d: merge of %d messages, %d ids: %.3f ms per batch, status %d" % (
     G, nn, int(tot[0]), e0.elapsed_time(e1) / steps, int(tot[1]) & 0xFFFFFFFF))
+c = (out_off[1:] - out_off[:-1]).to(torch.int64).cpu().numpy()
+print("ids per message: mean %.1f  p99 %d  max %d;  messages over 1024 ids: %d (%.1f %% of the ids), over 4096: %d (%.1f %%)" % (
+    c.mean(), int(np.percentile(c, 99)), int(c.max()), int((c > 1024).sum()), 100.0 * c[c > 1024].sum() / max(1, c.sum()),
+    int((c > 4096).sum()), 100.0 * c[c > 4096].sum() / max(1, c.sum())))
