@@ -434,11 +434,11 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   // lists of similar length that share nothing (the slices of a sharded exchange, several '#' patterns): staged and
   // merged pairwise in shared memory (kway.cuh)
   // (in a table: from four lists on, none of which dominates — otherwise streaming the longest and placing the others
-  // was measured faster; the slices of a sharded exchange: from three slices on always — placing means k - 1 searches
-  // in global memory per id there, and set the run time of k_write)
+  // was measured faster; the slices of a sharded exchange: always — placing means k - 1 searches in global memory per
+  // id there, and set the run time of k_write; two slices: 0.41 -> 0.26 ms per half batch against warp_merge2)
   else if (!dedup && k <= p.max_slots && ub <= (uint32_t)kKwayMax && p.max_small == (uint32_t)kRouteSmall &&
-           (p.slice_offsets ? k >= 3 : (k >= 4 && ub - mxlen >= 2u * mxlen && ub > 64u))) { cls = 5; cnt = ub; }
-  // two lists of similar length that share nothing: a symmetric merge through registers (warp_merge2)
+           (p.slice_offsets ? k >= 2 : (k >= 4 && ub - mxlen >= 2u * mxlen && ub > 64u))) { cls = 5; cnt = ub; }
+  // two lists of similar length that share nothing, too long for the above: a symmetric merge through registers (warp_merge2)
   // (slices of a sharded exchange only: in a table such pairs are rare, and the few long ones, merged by one warp in
   // dependent trips, set the run time of k_write_rest — measured: +0.005 ms on the headline batch)
   else if (p.slice_offsets && !dedup && k == 2 && k <= p.max_slots && 2u * (ub - mxlen) >= mxlen && ub > 64u && ub < (1u << 30) &&

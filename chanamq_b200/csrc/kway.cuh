@@ -17,7 +17,7 @@ namespace {
 constexpr int kKwayMax = 1280;   // ids of one message on this path (two buffers of that size per warp: 40 KB per CTA)
 
 struct __align__(16) KwayBuf {
-  uint32_t a[kKwayMax], b[kKwayMax];
+  uint32_t a[kKwayMax + 4], b[kKwayMax + 4];   // (+ 4: the merge loop reads one past a run before it looks at the index)
   uint32_t start[kRouteSlots + 2];   // run r = [start[r], start[r + 1]); entries past the last run = total
 };
 
@@ -64,22 +64,28 @@ __device__ __forceinline__ void warp_kway(const uint32_t* __restrict__ qlist, ui
         if (A[as + mid] < A[bs + (d - 1u - mid)]) l = mid + 1u; else h = mid;
       }
       uint32_t ia = as + l, ib = bs + (d - l);
-      uint32_t va = ia < bs ? A[ia] : kNone, vb = ib < eb ? A[ib] : kNone;
-      for (uint32_t pos = lo; pos < hi; ++pos) {
-        while (pos >= eb) {   // on to the next pair, from its beginning
-          ++pr;
-          ia = eb;
-          bs = kb.start[2 * pr + 1];
-          ib = bs;
-          eb = kb.start[2 * pr + 2];
-          va = ia < bs ? A[ia] : kNone;
-          vb = ib < eb ? A[ib] : kNone;
+      for (uint32_t pos = lo;;) {
+        // the part of the share inside this pair: a compare, a select and one load per id, nothing else in the loop
+        // (the load is unconditional: one past a run is still inside the buffers, and the value is not used)
+        const uint32_t seg = min(hi, eb);
+        uint32_t va = ia < bs ? A[ia] : kNone, vb = ib < eb ? A[ib] : kNone;   // (an exhausted run shows kNone, above every id)
+        for (; pos < seg; ++pos) {
+          const bool ta = va < vb;
+          B[pos] = ta ? va : vb;
+          ia += ta ? 1u : 0u;
+          ib += ta ? 0u : 1u;
+          const uint32_t nx = ta ? ia : ib;
+          const uint32_t got = A[nx];
+          const uint32_t v = nx < (ta ? bs : eb) ? got : kNone;
+          va = ta ? v : va;
+          vb = ta ? vb : v;
         }
-        const bool ta = va < vb;   // (an exhausted run shows kNone, above every id)
-        B[pos] = ta ? va : vb;
-        const uint32_t nx = ta ? ++ia : ++ib;
-        const uint32_t v = nx < (ta ? bs : eb) ? A[nx] : kNone;
-        if (ta) va = v; else vb = v;
+        if (pos >= hi) break;
+        ++pr;   // on to the next pair, from its beginning
+        ia = eb;
+        bs = kb.start[2 * pr + 1];
+        ib = bs;
+        eb = kb.start[2 * pr + 2];
       }
     }
     __syncwarp();
