@@ -83,3 +83,23 @@ def test_generator_is_deterministic_and_compiles_at_scale():
     st = m.stats()
     assert st["queues"] == 12_500 and 40_000 < st["groups"] <= st["bindings"] <= 50_000
     assert st["shapes"] < 120 and st["wstride"] == 8
+
+
+def test_three_byte_ids_host_side():  # chq_set_ids_format / chq_unpack_u24: the host half needs no GPU
+    import numpy as np
+    import pytest
+
+    from chanamq_b200 import ChqError
+    from chanamq_b200._lib import CHQ_IDS_U24, CHQ_IDS_U32
+    m = GpuMatcher(CHQ_TOPIC, CHQ_MODE_COMPAT, device=-1)
+    m.set_ids_format(CHQ_IDS_U24)
+    m.set_ids_format(CHQ_IDS_U32)
+    with pytest.raises(ChqError):
+        m.set_ids_format(2)
+    ids = np.array([0, 1, 255, 256, 65535, 65536, (1 << 24) - 1, 0x123456, 7], dtype=np.uint32)
+    packed = np.zeros(3 * len(ids), dtype=np.uint8)
+    for j, v in enumerate(ids.tolist()):  # the layout include/chanamq_gpu.h states: little-endian, back to back
+        packed[3 * j], packed[3 * j + 1], packed[3 * j + 2] = v & 255, (v >> 8) & 255, v >> 16
+    assert np.array_equal(m.unpack_u24(packed), ids)
+    assert len(m.unpack_u24(np.zeros(0, np.uint8))) == 0
+    m.close()
