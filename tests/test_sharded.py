@@ -109,14 +109,50 @@ def test_slices_on_one_gpu_merge_to_the_unsharded_oracle(g, p, nq):
     """G slice tables on one device (what G ranks would hold), routed one after the other, merged by
     chq_merge_slices_device: must equal the oracle over the whole table (4 bindings per queue in two of the
     cases: the same queue then sits in several slices and the union has to de-duplicate)."""
+    w, binds = _table(p, nq)
+    blob, off = w.keys(50_000, stream=21)
+    # one queue per binding (nq == p): no queue sits in two slices, the merge may skip the de-duplication
+    _merge_on_one_gpu(g, binds, blob, off, 1 if nq == p else 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("g", [2, 3, 8])
+def test_slices_with_long_results_merge_to_the_unsharded_oracle(g):
+    """Results around and beyond what warp_kway stages (1280 ids): 1200 and 4000 queues behind one pattern each, so a
+    message's ids are G runs of 150 ... 2000 — the shared-memory merge at its upper end, and what takes over from it
+    (two slices: warp_merge2; more: the long-list union)."""
+    pats, queues = [], []
+    for i in range(4000):
+        pats.append("big.#"); queues.append("b%05d" % ((i * 7) % 4000))
+    for i in range(1200):
+        pats.append("mid.*"); queues.append("m%05d" % ((i * 11) % 1200))
+    for i in range(1290):
+        pats.append("edge.*.x"); queues.append("e%05d" % i)
+    for i in range(40):
+        pats.append("#.few"); queues.append("f%05d" % i)
+    order = np.random.RandomState(5).permutation(len(pats))  # which slice a binding lands in: i mod G of this order
+    pb, poff = _pack([pats[i] for i in order])
+    qb, qoff = _pack([queues[i] for i in order])
+    binds = (pb, poff, qb, qoff, (order % 3 == 0).astype(np.uint8))
+    keys = ["big.a", "mid.z", "edge.k.x", "big", "mid", "mid.a.b", "big.few", "mid.few", "edge.q.x", "none", "a.few", "big.a.b.c"] * 40
+    blob, off = _pack(keys)
+    _merge_on_one_gpu(g, binds, blob, off, 1)
+
+
+def _pack(strings):
+    bs = [s.encode() for s in strings]
+    off = np.zeros(len(bs) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum([len(b) for b in bs])
+    return np.frombuffer(b"".join(bs) + b"\0", dtype=np.uint8).copy(), off
+
+
+def _merge_on_one_gpu(g, binds, blob, off, flags):
     torch = pytest.importorskip("torch")
     from chanamq_b200 import CHQ_MODE_SPEC, CHQ_TOPIC, GpuMatcher
     from chanamq_b200._lib import check, load_library
 
     L = load_library()
-    w, binds = _table(p, nq)
     whole = _oracle(binds)
-    blob, off = w.keys(50_000, stream=21)
     n = len(off) - 1
     dev = torch.device("cuda:0")
     st = torch.cuda.current_stream().cuda_stream
@@ -142,8 +178,6 @@ def test_slices_on_one_gpu_merge_to_the_unsharded_oracle(g, p, nq):
     out_off = torch.empty(n + 1, dtype=torch.int32, device=dev)
     out_ids = torch.empty(6_000_000, dtype=torch.int32, device=dev)
     out_dur = torch.empty(n, dtype=torch.uint8, device=dev)
-    # one queue per binding (nq == p): no queue sits in two slices, the merge may skip the de-duplication
-    flags = 1 if nq == p else 0
     check(L.chq_merge_slices_device2(0, all_off.data_ptr(), all_ids.data_ptr(), cap, all_dur.data_ptr(), g, n, out_off.data_ptr(),
                                      out_ids.data_ptr(), 6_000_000, out_dur.data_ptr(), tot.data_ptr() + 16 * g,
                                      tot.data_ptr() + 16 * g + 8, flags, st))
