@@ -422,10 +422,17 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
   int cls = 0;
   const bool dedup = (flags & kShared) != 0;
   // tiny: the whole result fits the 16-input sorting network of one thread (merge.cuh)
-  const bool tiny = !overflow && k >= 1 && k <= p.max_slots && ub <= (uint32_t)kTinyIds;
-  auto my_off = [&](uint32_t j) { return sm.loff[j][tid]; };
-  auto my_len = [&](uint32_t j) { return sm.llen[j][tid]; };
-  if (tiny) cnt = (k == 1 || !dedup) ? ub : tiny_union(tv.qlist, k, my_off, my_len, nullptr);
+  // (a headers exchange: up to 16 one-queue lists are the usual message; those past the slots are read where
+  // k_headers_match left them, here and in k_write — class 4 says so)
+  const bool tiny_desc = p.desc_k != nullptr && !overflow && k > p.max_slots && ub <= (uint32_t)kTinyIds;
+  const bool tiny = !overflow && k >= 1 && (k <= p.max_slots || tiny_desc) && ub <= (uint32_t)kTinyIds;
+  const uint2* dl = tiny_desc ? p.desc_lists + __ldg(p.desc_start + m) : nullptr;
+  auto my_off = [&](uint32_t j) { return dl ? __ldg(dl + j).x : sm.loff[j][tid]; };
+  auto my_len = [&](uint32_t j) { return dl ? __ldg(dl + j).y : sm.llen[j][tid]; };
+  if (tiny) {
+    cnt = (k == 1 || !dedup) ? ub : tiny_union(tv.qlist, k, my_off, my_len, nullptr);
+    if (tiny_desc) cls = 4;
+  }
   else if (overflow) cls = 2;
   else if (p.desc_k && k > p.max_slots && k <= (uint32_t)kRouteSmall && ub <= (uint32_t)kRouteSmall) { cls = 4; cnt = ub; }
   else if (k <= 1) cnt = ub;
@@ -472,7 +479,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_MIN_CTAS) k_probe(RoutePara
     }
     if (lane == src) { cnt = c; flags = fl; scr = so; }
   }
-  for (unsigned todo = __ballot_sync(kFull, cls == 4 && dedup); todo; todo &= todo - 1) {
+  for (unsigned todo = __ballot_sync(kFull, cls == 4 && dedup && !tiny); todo; todo &= todo - 1) {
     const int src = __ffs(todo) - 1;
     const uint32_t mm = __shfl_sync(kFull, m, src);
     const uint32_t c = warp_gather_small<false>(tv.qlist, p.desc_lists + __ldg(p.desc_start + mm), __shfl_sync(kFull, k, src),
@@ -689,6 +696,7 @@ __global__ void __launch_bounds__(kRouteThreads, CHQ_WRITE_CTAS) k_write(RoutePa
     const bool live = cnt > 0 && fits;
     if (!(CHQ_EXP & 4) && live && (meta & kMetaTiny)) {
       const uint2* lists = p.mlist + (size_t)m * kRouteSlots;
+      if (((meta >> 8) & 15u) == 4u) lists = p.desc_lists + __ldg(lists).x;   // headers exchange: the lists stayed in the descriptor arena
       auto off = [&](uint32_t j) { return __ldg(lists + j).x; };
       auto len = [&](uint32_t j) { return __ldg(lists + j).y; };
       tiny_union(ql, meta & 0xFF, off, len, p.ids + pos);
