@@ -103,3 +103,33 @@ def test_three_byte_ids_host_side():  # chq_set_ids_format / chq_unpack_u24: the
     assert np.array_equal(m.unpack_u24(packed), ids)
     assert len(m.unpack_u24(np.zeros(0, np.uint8))) == 0
     m.close()
+
+
+def test_header_is_plain_c():
+    """The boundary is a C ABI: include/*.h must compile as C99 on its own (what a cgo / JNI / JNA generator is fed)."""
+    import glob
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for h in sorted(glob.glob(os.path.join(root, "include", "*.h"))):
+        out = subprocess.run(["gcc", "-x", "c", "-std=c99", "-fsyntax-only", "-Wall", "-Wextra", "-pedantic", "-Werror", h],
+                             capture_output=True, text=True)
+        assert out.returncode == 0, out.stderr
+
+
+def test_c99_consumer_links_and_runs(tmp_path):
+    """tests/c_consumer.c: the host half of the boundary driven from plain C through the shared library, no Python in between"""
+    import os
+    import subprocess
+
+    from chanamq_b200 import build
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.dirname(build.build_product())
+    exe = str(tmp_path / "c_consumer")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(root, "include"),
+                    os.path.join(root, "tests", "c_consumer.c"), "-o", exe, "-L", lib_dir, "-lchanagpu", "-Wl,-rpath," + lib_dir],
+                   check=True, capture_output=True, text=True)
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0 and out.stdout.strip() == "ok", out.stdout + out.stderr
